@@ -1,0 +1,141 @@
+/*
+ * mfa_b200.h -- C-ABI of the B200-native (sm_100a) attention-forward library.
+ *
+ * This is the drop-in boundary for the reference's extension surface
+ *   /root/reference/csrc/api.cpp:4-9            (pybind: the three _C functions)
+ *   /root/reference/csrc/mfa/api.h:8-40         (their C++ prototypes)
+ *   /root/reference/csrc/mfa/flash.h:8-77       (ForwardParams + the two launchers)
+ * restated with plain pointers and sizes: no torch types, no C++ types.  The caller owns all
+ * memory (inputs, output, workspaces); every call is asynchronous on the given CUDA stream and
+ * returns an error code instead of aborting the process (the reference exit(1)s on CUDA errors,
+ * csrc/mfa/api.cpp:16-24 -- deliberately not replicated).
+ *
+ * All strides are in ELEMENTS (fp16/bf16), exactly like ForwardParams (flash.h:17-31).
+ * The last (head_dim) dimension must be contiguous (api.cpp:135-137).
+ */
+#ifndef MFA_B200_H_
+#define MFA_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MFA_B200_ABI_VERSION 1
+
+/* error codes (0 == success).  mfa_last_error() returns the message of the last failure on the
+ * calling thread. */
+enum {
+    MFA_OK = 0,
+    MFA_ERR_INVALID_ARG = 1,   /* shape / dtype / alignment contract violated (TORCH_CHECK analogue) */
+    MFA_ERR_UNSUPPORTED = 2,   /* e.g. head_dim not a multiple of 8 or > 256, page size not usable */
+    MFA_ERR_CUDA = 3,          /* a CUDA runtime / driver call failed (message has the CUDA string) */
+    MFA_ERR_NO_DEVICE = 4      /* not an sm_100 device */
+};
+
+/*
+ * POD mirror of mfa::ForwardParams (/root/reference/csrc/mfa/flash.h:8-73).
+ * Field meaning is identical unless noted.  Zero-initialise, then fill.
+ */
+typedef struct mfa_params {
+    /* device pointers (fp16 or bf16, see is_bf16) -- flash.h:11-14 */
+    const void* q_ptr;
+    const void* k_ptr;
+    const void* v_ptr;
+    void*       o_ptr;
+
+    /* element strides -- flash.h:16-30.  batch strides are ignored when cu_seqlens_q != NULL
+     * (packed varlen) and, for K/V, when block_table != NULL (paged). */
+    int64_t q_batch_stride, q_head_stride, q_row_stride;
+    int64_t k_batch_stride, k_head_stride, k_row_stride;
+    int64_t v_batch_stride, v_head_stride, v_row_stride;
+    int64_t o_batch_stride, o_head_stride, o_row_stride;
+
+    int32_t is_causal;          /* top-left aligned: key col masked iff col > row (prefill.cuh:416) */
+    int32_t window_size_left;   /* accepted and ignored, like the reference (flash.h:33-34) */
+    int32_t window_size_right;
+
+    int32_t heads;              /* query heads */
+    int32_t kv_heads;           /* heads % kv_heads == 0; kv_head = head / (heads/kv_heads) (prefill.cuh:49) */
+    int32_t batch;
+    int32_t seqlen_q;           /* fixed-length: Sq ; varlen: max_seqlen_q ; decode: 1 */
+    int32_t seqlen_k;           /* fixed-length: Sk ; varlen: max_seqlen_k ; decode: cache capacity in rows */
+    int32_t head_dim;           /* <= 256, multiple of 8 */
+    int32_t is_bf16;            /* 0 = fp16, 1 = bf16 */
+    float   softmax_scale;      /* 0 => 1/sqrt(head_dim) (the reference's only choice, api.cpp:99) */
+
+    /* packed variable-length batches -- flash.h:49-54 (int32, batch+1 entries, device memory) */
+    const int32_t* cu_seqlens_q;
+    const int32_t* cu_seqlens_k;
+    int32_t total_q;            /* rows in the packed q / o tensors (varlen only) */
+    int32_t total_k;            /* rows in the packed k / v tensors (varlen, non-paged only) */
+
+    /* paged KV -- flash.h:57-61.  k/v are (num_blocks, page_block_size, kv_heads, head_dim) */
+    const int32_t* block_table;          /* (batch, max_blocks_per_seq) int32, device */
+    int32_t block_table_batch_stride;    /* elements */
+    int32_t max_blocks_per_seq;
+    int32_t page_block_size;
+    int32_t num_blocks;
+    int64_t k_cache_block_stride;        /* elements */
+    int64_t v_cache_block_stride;
+
+    /* decode -- flash.h:64-72 */
+    const int32_t* seqlens_k;   /* (batch) int32 device; NULL => every row attends to seqlen_k keys */
+    int32_t num_splits;         /* <= 0: heuristic ; clamped to the number of 64-row KV blocks (api.cpp:320-327) */
+    float*  softmax_lse_ptr;    /* optional (batch, heads) fp32 natural-log LSE output, may be NULL */
+
+    /* multi-GPU KV-sharded decode: when partial_out != 0 the decode writes a NORMALISED fp32
+     * partial O (batch, heads, head_dim) to o_ptr instead of fp16/bf16, and softmax_lse_ptr
+     * (required) receives the partial LSE (-inf for empty shards).  New; no reference analogue. */
+    int32_t partial_out;
+    int32_t reserved0;
+} mfa_params_t;
+
+/* --- introspection ------------------------------------------------------------------------ */
+int         mfa_abi_version(void);
+const char* mfa_last_error(void);
+/* 1 if the current device is compute capability 10.x, else 0 */
+int         mfa_device_supported(void);
+
+/* --- prefill: replaces mfa::run_flash_attention_forward (flash.h:76, flash.cu:74-82) ---------
+ * Fixed-length (cu_seqlens_q == NULL), packed varlen (cu_seqlens_* != NULL) and varlen with paged
+ * K/V (block_table != NULL) in one entry point, like the reference. */
+int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream);
+
+/* --- decode (q_len == 1): replaces mfa::run_flash_attention_with_kv_cache (flash.h:77,
+ *     flash.cu:85-93) plus forward_params_set_split_kv (api.cpp:305-340). ----------------------
+ * mfa_decode_num_splits: the split count the library will use for this problem
+ *   (requested <= 0 => heuristic; result clamped to ceil(seqlen_k / 64) like api.cpp:325-327).
+ * mfa_decode_workspace_bytes: bytes of scratch needed for that split count (0 when 1 split).
+ * mfa_decode_fwd: launches split-KV kernel (+ LSE combine when splits > 1) on the stream.
+ *   `workspace` must hold mfa_decode_workspace_bytes(...) bytes; it needs no initialisation. */
+int    mfa_decode_num_splits(const mfa_params_t* p);
+size_t mfa_decode_workspace_bytes(const mfa_params_t* p, int num_splits);
+int    mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_bytes, void* cuda_stream);
+
+/* --- LSE merge of R normalised partial results (the consumer of the multi-GPU all-gather and
+ *     the same arithmetic as the reference's combine kernel, decode.cuh:665-755, but with a
+ *     max-subtracted log-sum-exp).
+ *   packed: (R, rows, head_dim + 1) fp32, per row [O_0 .. O_{D-1}, LSE]   (rows = batch*heads)
+ *   out:    (rows, head_dim) fp16/bf16 with row stride out_row_stride (elements)
+ *   lse_out: optional (rows) fp32 */
+int mfa_combine_partials(const float* packed, int num_partials, int rows, int head_dim,
+                         void* out, int64_t out_row_stride, int is_bf16, float* lse_out,
+                         void* cuda_stream);
+
+/* number of kernel launches issued by this library since load (bench.py reports it) */
+uint64_t mfa_launch_count(void);
+
+/* --- single-tile tcgen05 self test (tests/ only; isolates UMMA descriptor / TMEM layout conventions)
+ *   mode 0: d[128 x 128] = a[128 x kdim] * b[128 x kdim]^T     (kdim 64 or 128; the Q K^T shape)
+ *   mode 1: d[128 x ncols] = a[128 x 128] * b[128 x ncols]     (a staged in TMEM; the P V shape)
+ *   a, b: 16-bit row-major device buffers; d: fp32 row-major; lbo/sbo: 0 = library defaults. */
+int mfa_selftest_umma(int mode, const void* a, const void* b, float* d, int kdim, int ncols, int is_bf16,
+                      uint32_t lbo, uint32_t sbo, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MFA_B200_H_ */

@@ -1,0 +1,301 @@
+"""Host boundary: the three extension functions of the reference, re-implemented over the C-ABI.
+
+Same names, positional signatures, argument meaning and error behaviour as the reference's pybind module
+``mini_flash_attention._C`` (/root/reference/csrc/api.cpp:4-9, typed in mini_flash_attention/_C.pyi:4-41),
+whose bodies live in /root/reference/csrc/mfa/api.cpp:
+
+    mini_flash_attention_forward          <- mfa::flash_attention_forward          api.cpp:113-186
+    mini_flash_attention_varlen_forward   <- mfa::flash_attention_varlen_forward   api.cpp:189-267
+    mini_flash_attention_with_kvcache     <- mfa::mha_fwd_kvcache                  api.cpp:343-446
+
+PyTorch is used for device memory (outputs, split workspaces through the caching allocator), the current
+stream and the device guard -- plumbing only.  All arithmetic happens in libmfa_b200.so (hand-written
+sm_100a kernels).  There is no CPU path: non-CUDA tensors raise RuntimeError like the reference's
+CHECK_DEVICE (api.cpp:7, 131-133).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Union
+
+import torch
+
+from . import _lib
+from ._lib import MfaParams
+
+
+def _check(cond: bool, msg: str) -> None:
+    if not cond:  # TORCH_CHECK => RuntimeError
+        raise RuntimeError(msg)
+
+
+def _check_qkv(q, k, v) -> None:
+    # api.cpp:125-137
+    _check(q.dtype in (torch.float16, torch.bfloat16), "FlashAttention only support fp16 and bf16 data type")
+    _check(k.dtype == q.dtype, "query and key must have the same dtype")
+    _check(v.dtype == q.dtype, "query and value must have the same dtype")
+    _check(q.is_cuda, "q must be on CUDA")
+    _check(k.is_cuda, "k must be on CUDA")
+    _check(v.is_cuda, "v must be on CUDA")
+    _check(q.stride(-1) == 1, "Input tensor must have contiguous last dimension")
+    _check(k.stride(-1) == 1, "Input tensor must have contiguous last dimension")
+    _check(v.stride(-1) == 1, "Input tensor must have contiguous last dimension")
+
+
+def _tma_ok(t: torch.Tensor) -> bool:
+    """TMA needs a 16-byte aligned base and 16-byte multiples for every non-innermost stride."""
+    if t.data_ptr() % 16:
+        return False
+    return all(s % 8 == 0 for s in t.stride()[:-1])
+
+
+def _tma_ready(t: torch.Tensor) -> torch.Tensor:
+    return t if _tma_ok(t) else t.contiguous()
+
+
+def _check_head_dim(head_dim: int, num_heads: int, kv_num_heads: int) -> None:
+    _check(head_dim <= 256, "head dimension must be less than or equal to 256")  # api.cpp:152
+    _check(kv_num_heads > 0 and num_heads % kv_num_heads == 0,
+           "number of key/value heads must be divisible by number of query heads")  # api.cpp:153
+    # The reference rounds head_dim up to a multiple of 32 and then reads the neighbouring head
+    # (static_switch.h:25-52); we refuse instead of returning wrong numbers.
+    _check(head_dim % 8 == 0, "head dimension must be a multiple of 8")
+
+
+def _stream_ptr(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _i32_ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, window_size_right):
+    """Fixed-length prefill.  q (B,Sq,H,D); k, v (B,Sk,Hkv,D); returns (B,Sq,H,D).  api.cpp:113-186."""
+    _check_qkv(q, k, v)
+    _check(q.dim() == 4 and k.dim() == 4 and v.dim() == 4, "q, k, v must be 4-D (batch, seqlen, heads, head_dim)")
+    batch, seqlen_q, num_heads, head_dim = q.shape
+    seqlen_k, kv_num_heads = k.shape[1], k.shape[2]
+    _check(k.shape[0] == batch, "batch size of q and k must be the same")
+    _check(v.shape[0] == batch, "batch size of q and v must be the same")
+    _check(v.shape[1] == seqlen_k, "sequence length of k must be the same as v")
+    _check_head_dim(head_dim, num_heads, kv_num_heads)
+    _check(tuple(k.shape) == (batch, seqlen_k, kv_num_heads, head_dim), "k must have shape (batch, seqlen_k, kv_num_heads, head_dim)")
+    _check(tuple(v.shape) == (batch, seqlen_k, kv_num_heads, head_dim), "v must have shape (batch, seqlen_k, kv_num_heads, head_dim)")
+    if out is not None:
+        _check(out.stride(-1) == 1, "Output tensor must have contiguous last dimension")
+        _check(tuple(out.shape) == (batch, seqlen_q, num_heads, head_dim), "out must have shape (batch, seqlen_q, num_heads, head_dim)")
+        _check(out.dtype == q.dtype and out.is_cuda, "out must match q's dtype and device")
+    else:
+        out = torch.empty_like(q)
+    if batch == 0 or seqlen_q == 0 or num_heads == 0:
+        return out
+    if seqlen_k == 0:
+        return out.zero_()
+    qc, kc, vc = _tma_ready(q), _tma_ready(k), _tma_ready(v)
+    oc = out if _tma_ok(out) else torch.empty(out.shape, dtype=out.dtype, device=out.device)
+
+    P = MfaParams()
+    P.q_ptr, P.k_ptr, P.v_ptr, P.o_ptr = qc.data_ptr(), kc.data_ptr(), vc.data_ptr(), oc.data_ptr()
+    P.q_batch_stride, P.q_row_stride, P.q_head_stride = qc.stride(0), qc.stride(1), qc.stride(2)
+    P.k_batch_stride, P.k_row_stride, P.k_head_stride = kc.stride(0), kc.stride(1), kc.stride(2)
+    P.v_batch_stride, P.v_row_stride, P.v_head_stride = vc.stride(0), vc.stride(1), vc.stride(2)
+    P.o_batch_stride, P.o_row_stride, P.o_head_stride = oc.stride(0), oc.stride(1), oc.stride(2)
+    P.is_causal = int(bool(is_causal))  # api.cpp:157, :88
+    P.window_size_left, P.window_size_right = int(window_size_left), int(window_size_right)
+    P.heads, P.kv_heads, P.batch = num_heads, kv_num_heads, batch
+    P.seqlen_q, P.seqlen_k, P.head_dim = seqlen_q, seqlen_k, head_dim
+    P.is_bf16 = int(q.dtype == torch.bfloat16)
+    with torch.cuda.device(q.device):  # api.cpp:123
+        _lib.check(_lib.load().mfa_prefill_fwd(ctypes.byref(P), _stream_ptr(q.device)), "mfa_prefill_fwd")
+    if oc is not out:
+        out.copy_(oc)
+    return out
+
+
+def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal,
+                                        window_size_left, window_size_right, block_table):
+    """Packed variable-length prefill, optionally with paged K/V.  api.cpp:189-267.
+
+    q (total_q,H,D); k, v (total_k,Hkv,D) or, with block_table (batch,max_blocks) int32,
+    (num_blocks,page,Hkv,D).  Superset of the reference: total_k may differ from total_q (quirk Q4)."""
+    _check_qkv(q, k, v)
+    _check(cu_seqlens_q.is_cuda, "cu_seqlens_q must be on CUDA")
+    _check(cu_seqlens_k.is_cuda, "cu_seqlens_k must be on CUDA")
+    _check(cu_seqlens_q.dtype == torch.int32 and cu_seqlens_k.dtype == torch.int32, "cu_seqlens must be int32")
+    _check(q.dim() == 3, "q must have shape (total_q, num_heads, head_dim)")
+    total_q, num_heads, head_dim = q.shape
+    batch = cu_seqlens_q.numel() - 1
+    _check(batch >= 0 and cu_seqlens_k.numel() == batch + 1, "cu_seqlens_q and cu_seqlens_k must have batch+1 entries")
+    kv_num_heads = k.shape[-2]
+    _check_head_dim(head_dim, num_heads, kv_num_heads)
+    out = torch.empty_like(q)
+    if batch == 0 or total_q == 0 or num_heads == 0:
+        return out
+    cu_q, cu_k = cu_seqlens_q.contiguous(), cu_seqlens_k.contiguous()
+
+    P = MfaParams()
+    if block_table is not None:
+        _check(k.dim() == 4 and v.dim() == 4, "paged k/v must have shape (num_blocks, page_block_size, kv_heads, head_dim)")
+        num_blocks, page = k.shape[0], k.shape[1]
+        _check(tuple(k.shape) == (num_blocks, page, kv_num_heads, head_dim), "k must have shape (num_blocks, page_block_size, kv_num_heads, head_dim)")
+        _check(tuple(v.shape) == (num_blocks, page, kv_num_heads, head_dim), "v must have shape (num_blocks, page_block_size, kv_num_heads, head_dim)")
+        _check(block_table.is_cuda, "block_table must be on CUDA")
+        _check(block_table.dtype == torch.int32, "block_table must be int32")
+        _check(block_table.dim() == 2 and block_table.shape[0] == batch, "block_table must have the same batch size as q")
+        bt = block_table if block_table.stride(1) == 1 else block_table.contiguous()
+        kc, vc = _tma_ready(k), _tma_ready(v)
+        P.block_table = bt.data_ptr()
+        P.block_table_batch_stride = bt.stride(0)
+        P.max_blocks_per_seq = bt.shape[1]
+        P.page_block_size, P.num_blocks = page, num_blocks
+        P.k_cache_block_stride, P.v_cache_block_stride = kc.stride(0), vc.stride(0)
+        P.k_row_stride, P.k_head_stride = kc.stride(1), kc.stride(2)
+        P.v_row_stride, P.v_head_stride = vc.stride(1), vc.stride(2)
+    else:
+        _check(k.dim() == 3 and v.dim() == 3, "k, v must have shape (total_k, kv_num_heads, head_dim)")
+        total_k = k.shape[0]
+        _check(tuple(k.shape) == (total_k, kv_num_heads, head_dim), "k must have shape (total_k, kv_num_heads, head_dim)")
+        _check(tuple(v.shape) == (total_k, kv_num_heads, head_dim), "v must have shape (total_k, kv_num_heads, head_dim)")
+        if total_k == 0:
+            return out.zero_()
+        kc, vc = _tma_ready(k), _tma_ready(v)
+        P.total_k = total_k
+        P.k_row_stride, P.k_head_stride = kc.stride(0), kc.stride(1)
+        P.v_row_stride, P.v_head_stride = vc.stride(0), vc.stride(1)
+    qc = _tma_ready(q)
+    P.q_ptr, P.k_ptr, P.v_ptr, P.o_ptr = qc.data_ptr(), kc.data_ptr(), vc.data_ptr(), out.data_ptr()
+    P.q_row_stride, P.q_head_stride = qc.stride(0), qc.stride(1)
+    P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1)
+    P.is_causal = int(bool(causal))  # api.cpp:231
+    P.window_size_left, P.window_size_right = int(window_size_left), int(window_size_right)
+    P.heads, P.kv_heads, P.batch = num_heads, kv_num_heads, batch
+    P.seqlen_q, P.seqlen_k, P.head_dim = int(max_seqlen_q), int(max_seqlen_k), head_dim
+    P.is_bf16 = int(q.dtype == torch.bfloat16)
+    P.cu_seqlens_q, P.cu_seqlens_k = cu_q.data_ptr(), cu_k.data_ptr()
+    P.total_q = total_q
+    with torch.cuda.device(q.device):
+        _lib.check(_lib.load().mfa_prefill_fwd(ctypes.byref(P), _stream_ptr(q.device)), "mfa_prefill_fwd")
+    return out
+
+
+def _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits):
+    """Validation + parameter block shared by the decode entry points.  api.cpp:343-433."""
+    _check_qkv(q, k_cache, v_cache)
+    _check(q.dim() == 4, "q must have shape (batch, 1, num_heads, head_dim)")
+    batch, seqlen_q, num_heads, head_dim = q.shape
+    _check(seqlen_q == 1, f"flash decoding expects seqlen_q == 1, got {seqlen_q}")  # api.cpp:377
+    kv_num_heads = k_cache.shape[-2]
+    _check_head_dim(head_dim, num_heads, kv_num_heads)
+    _check(k_cache.dim() == 4 and v_cache.dim() == 4, "k_cache / v_cache must be 4-D")
+    keep = []
+    P = MfaParams()
+    kc, vc = _tma_ready(k_cache), _tma_ready(v_cache)
+    if block_table is not None:
+        _check(block_table.is_cuda, "block_table must be on CUDA")
+        _check(block_table.dtype == torch.int32, "block_table must be int32")
+        _check(block_table.dim() == 2 and block_table.shape[0] == batch, "block_table must have the same batch size as q")
+        num_blocks, page = k_cache.shape[0], k_cache.shape[1]
+        _check(tuple(k_cache.shape) == (num_blocks, page, kv_num_heads, head_dim), "k_cache must have shape (num_blocks, page_block_size, kv_num_heads, head_dim)")
+        _check(tuple(v_cache.shape) == (num_blocks, page, kv_num_heads, head_dim), "v_cache must have shape (num_blocks, page_block_size, kv_num_heads, head_dim)")
+        bt = block_table if block_table.stride(1) == 1 else block_table.contiguous()
+        keep.append(bt)
+        seqlen_k = bt.shape[1] * page  # api.cpp:392-394
+        P.block_table = bt.data_ptr()
+        P.block_table_batch_stride = bt.stride(0)
+        P.max_blocks_per_seq = bt.shape[1]
+        P.page_block_size, P.num_blocks = page, num_blocks
+        P.k_cache_block_stride, P.v_cache_block_stride = kc.stride(0), vc.stride(0)
+    else:
+        seqlen_k = k_cache.shape[1]
+        _check(tuple(k_cache.shape) == (batch, seqlen_k, kv_num_heads, head_dim), "k_cache must have shape (batch, seqlen_k, kv_num_heads, head_dim)")
+        _check(tuple(v_cache.shape) == (batch, seqlen_k, kv_num_heads, head_dim), "v_cache must have shape (batch, seqlen_k, kv_num_heads, head_dim)")
+        P.k_batch_stride, P.v_batch_stride = kc.stride(0), vc.stride(0)
+    P.k_row_stride, P.k_head_stride = kc.stride(1), kc.stride(2)
+    P.v_row_stride, P.v_head_stride = vc.stride(1), vc.stride(2)
+    # cache_seqlens: tensor (reference), or -- superset, SURVEY quirk Q5 -- None (full cache) / int (broadcast)
+    if cache_seqlens is None:
+        P.seqlens_k = None
+    else:
+        if isinstance(cache_seqlens, int):
+            cache_seqlens = torch.full((batch,), cache_seqlens, dtype=torch.int32, device=q.device)
+        _check(cache_seqlens.is_cuda, "seqlens_k must be on CUDA")
+        _check(cache_seqlens.dtype == torch.int32, "seqlens_k must be int32")  # api.cpp:430
+        _check(cache_seqlens.numel() == batch, "seqlens_k must have the same number of elements as batch size")
+        sl = cache_seqlens.contiguous()
+        keep.append(sl)
+        P.seqlens_k = sl.data_ptr()
+    qc = q if (q.data_ptr() % 4 == 0 and q.stride(0) % 2 == 0 and q.stride(2) % 2 == 0) else q.contiguous()
+    keep += [qc, kc, vc]
+    P.q_ptr, P.k_ptr, P.v_ptr = qc.data_ptr(), kc.data_ptr(), vc.data_ptr()
+    P.q_batch_stride, P.q_row_stride, P.q_head_stride = qc.stride(0), qc.stride(1), qc.stride(2)
+    P.heads, P.kv_heads, P.batch = num_heads, kv_num_heads, batch
+    P.seqlen_q, P.seqlen_k, P.head_dim = 1, seqlen_k, head_dim
+    P.is_bf16 = int(q.dtype == torch.bfloat16)
+    P.num_splits = int(num_splits)
+    return P, keep
+
+
+def mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens: Optional[Union[int, torch.Tensor]],
+                                      block_table, causal, num_splits=0):
+    """q_len == 1 decode over a contiguous or paged KV cache.  api.cpp:343-446.
+    `causal` is accepted and ignored exactly like the reference (api.cpp:349, quirk Q10)."""
+    P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
+    out = torch.empty_like(q)  # api.cpp:405
+    if q.numel() == 0:
+        return out
+    if P.seqlen_k == 0:
+        return out.zero_()
+    oc = out if (out.data_ptr() % 8 == 0 and out.stride(0) % 4 == 0 and out.stride(2) % 4 == 0) else \
+        torch.empty(out.shape, dtype=out.dtype, device=out.device)
+    P.o_ptr = oc.data_ptr()
+    P.o_batch_stride, P.o_row_stride, P.o_head_stride = oc.stride(0), oc.stride(1), oc.stride(2)
+    lib = _lib.load()
+    with torch.cuda.device(q.device):
+        splits = lib.mfa_decode_num_splits(ctypes.byref(P))
+        _check(splits >= 1, "mfa_decode_num_splits failed")
+        P.num_splits = splits
+        ws_bytes = lib.mfa_decode_workspace_bytes(ctypes.byref(P), splits)
+        ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=q.device) if ws_bytes else None  # api.cpp:333-334
+        _lib.check(lib.mfa_decode_fwd(ctypes.byref(P), ws.data_ptr() if ws is not None else None, ws_bytes,
+                                      _stream_ptr(q.device)), "mfa_decode_fwd")
+    if oc is not out:
+        out.copy_(oc)
+    return out
+
+
+def decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits=0):
+    """KV-shard building block of the multi-GPU decode: normalised fp32 partial O (B,H,D) and LSE (B,H)
+    over this rank's part of the KV axis (LSE = -inf, O = 0 where the shard is empty).  New -- the reference
+    has no multi-GPU path; the arithmetic is its split-KV partial (decode.cuh:645-661)."""
+    P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
+    batch, _, num_heads, head_dim = q.shape
+    o = torch.empty(batch, num_heads, head_dim, dtype=torch.float32, device=q.device)
+    lse = torch.empty(batch, num_heads, dtype=torch.float32, device=q.device)
+    P.o_ptr, P.softmax_lse_ptr, P.partial_out = o.data_ptr(), lse.data_ptr(), 1
+    lib = _lib.load()
+    with torch.cuda.device(q.device):
+        splits = lib.mfa_decode_num_splits(ctypes.byref(P))
+        _check(splits >= 1, "mfa_decode_num_splits failed")
+        P.num_splits = splits
+        ws_bytes = lib.mfa_decode_workspace_bytes(ctypes.byref(P), splits)
+        ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=q.device) if ws_bytes else None
+        _lib.check(lib.mfa_decode_fwd(ctypes.byref(P), ws.data_ptr() if ws is not None else None, ws_bytes,
+                                      _stream_ptr(q.device)), "mfa_decode_fwd")
+    return o, lse
+
+
+def combine_partials(packed: torch.Tensor, out_dtype: torch.dtype, return_lse: bool = False):
+    """LSE merge of R packed partials (R, rows, D+1) fp32 -> (rows, D) out_dtype.  decode.cuh:665-755."""
+    _check(packed.is_cuda and packed.dtype == torch.float32 and packed.dim() == 3, "packed must be a CUDA fp32 (R, rows, D+1) tensor")
+    _check(out_dtype in (torch.float16, torch.bfloat16), "out dtype must be fp16 or bf16")
+    packed = packed.contiguous()
+    R, rows, d1 = packed.shape
+    out = torch.empty(rows, d1 - 1, dtype=out_dtype, device=packed.device)
+    lse = torch.empty(rows, dtype=torch.float32, device=packed.device) if return_lse else None
+    with torch.cuda.device(packed.device):
+        _lib.check(_lib.load().mfa_combine_partials(packed.data_ptr(), R, rows, d1 - 1, out.data_ptr(), out.stride(0),
+                                                    int(out_dtype == torch.bfloat16),
+                                                    lse.data_ptr() if lse is not None else None,
+                                                    _stream_ptr(packed.device)), "mfa_combine_partials")
+    return (out, lse) if return_lse else out

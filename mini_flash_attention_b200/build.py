@@ -1,0 +1,80 @@
+"""In-tree build of libmfa_b200.so (sm_100a only) with plain nvcc.
+
+    python -m mini_flash_attention_b200.build [--force] [--verbose]
+
+The shared library exports exactly the C-ABI declared in include/mfa_b200.h.  It is built next to this
+file (git-ignored, but shipped to the GPU box by gpurun) so that the loaded .so is visibly in-tree.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(PKG_DIR, "csrc")
+REPO = os.path.dirname(PKG_DIR)
+LIB_PATH = os.path.join(PKG_DIR, "libmfa_b200.so")
+OBJ_DIR = os.path.join(PKG_DIR, "_obj")
+
+SOURCES = ["capi.cu", "tmap.cu", "decode_sm100.cu", "prefill_sm100.cu", "selftest_sm100.cu"]
+HEADERS = ["kparams.h", "ptx.cuh", "tmap.h", os.path.join(REPO, "include", "mfa_b200.h")]
+
+NVCC_FLAGS = [
+    "-std=c++17", "-O3", "-lineinfo", "--use_fast_math",
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-Xcompiler", "-fPIC",
+    "--expt-relaxed-constexpr",
+]
+
+
+def _nvcc() -> str:
+    cand = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "bin", "nvcc")
+    return cand if os.path.exists(cand) else "nvcc"
+
+
+def _stale(target: str, deps) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+    hdrs = [h if os.path.isabs(h) else os.path.join(CSRC, h) for h in HEADERS]
+    if not force and not _stale(LIB_PATH, srcs + hdrs + [os.path.abspath(__file__)]):
+        return LIB_PATH
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    nvcc = _nvcc()
+    t0 = time.time()
+
+    def compile_one(src: str):
+        obj = os.path.join(OBJ_DIR, os.path.basename(src) + ".o")
+        if not force and not _stale(obj, [src] + hdrs + [os.path.abspath(__file__)]):
+            return obj, 0, ""
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-I", CSRC, "-c", src, "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        return obj, r.returncode, r.stdout + r.stderr
+
+    with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
+        results = list(ex.map(compile_one, srcs))
+    for obj, rc, out in results:
+        if verbose and out:
+            print(out)
+        if rc != 0:
+            raise RuntimeError(f"nvcc failed for {obj}:\n{out}")
+    link = [nvcc, "-shared", "-o", LIB_PATH] + [o for o, _, _ in results] + ["-gencode", "arch=compute_100a,code=sm_100a"]
+    r = subprocess.run(link, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(f"[mfa_b200] built {LIB_PATH} in {time.time() - t0:.1f}s")
+    return LIB_PATH
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv, verbose="--verbose" in sys.argv or "-v" in sys.argv)
+    print(LIB_PATH)

@@ -1,0 +1,382 @@
+// capi.cu -- the extern "C" boundary declared in include/mfa_b200.h.
+//
+// Host-side equivalent of the reference's L1/L2 layers: ForwardParams interpretation
+// (/root/reference/csrc/mfa/api.cpp:30-101), dispatch on dtype x head_dim x {fixed | varlen | paged}
+// (/root/reference/csrc/mfa/flash.cu:74-93, static_switch.h:3-52), the split-KV heuristic and workspace
+// layout (api.cpp:269-340), and launch.  Every failure is reported through a return code +
+// mfa_last_error(); nothing here aborts the process and nothing falls back to a CPU path.
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/mfa_b200.h"
+#include "kparams.h"
+#include "tmap.h"
+
+namespace mfa {
+cudaError_t launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeKParams& p, bool is_bf16,
+                          int dpad, cudaStream_t stream);
+cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream);
+cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                           const PrefillKParams& p, bool is_bf16, int dpad, cudaStream_t stream);
+int prefill_rows_per_cta(int dpad);
+}  // namespace mfa
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    return fail(MFA_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+int gcd_int(int a, int b) {
+    while (b) {
+        int t = a % b;
+        a = b;
+        b = t;
+    }
+    return a;
+}
+
+int sm_count() {
+    static int cached[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (!cached[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+int check_device() {
+    static int ok[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    if (dev >= 0 && dev < 64 && ok[dev]) return MFA_OK;
+    int major = 0;
+    e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+    if (major != 10) return fail(MFA_ERR_NO_DEVICE, "mfa_b200 kernels are sm_100a only; device %d is sm_%d", dev, major * 10);
+    if (dev >= 0 && dev < 64) ok[dev] = 1;
+    return MFA_OK;
+}
+
+int dpad_of(int d) { return d <= 64 ? 64 : (d <= 128 ? 128 : 256); }
+
+// checks shared by every entry point (api.cpp:126-153)
+int check_common(const mfa_params_t* p) {
+    if (!p) return fail(MFA_ERR_INVALID_ARG, "params is NULL");
+    if (!p->q_ptr || !p->k_ptr || !p->v_ptr || !p->o_ptr) return fail(MFA_ERR_INVALID_ARG, "q/k/v/o pointers must be non-NULL");
+    if (p->head_dim <= 0 || p->head_dim > 256)
+        return fail(MFA_ERR_INVALID_ARG, "head dimension must be less than or equal to 256 (got %d)", p->head_dim);
+    if (p->head_dim % 8) return fail(MFA_ERR_UNSUPPORTED, "head dimension must be a multiple of 8 (got %d)", p->head_dim);
+    if (p->heads <= 0 || p->kv_heads <= 0 || p->heads % p->kv_heads)
+        return fail(MFA_ERR_INVALID_ARG, "number of key/value heads must be divisible by number of query heads (%d %% %d)",
+                    p->heads, p->kv_heads);
+    if (p->batch <= 0) return fail(MFA_ERR_INVALID_ARG, "batch must be positive");
+    return MFA_OK;
+}
+
+bool mult8(int64_t x) { return (x % 8) == 0; }
+
+}  // namespace
+
+extern "C" {
+
+int mfa_abi_version(void) { return MFA_B200_ABI_VERSION; }
+const char* mfa_last_error(void) { return g_err; }
+uint64_t mfa_launch_count(void) { return g_launches.load(); }
+
+int mfa_device_supported(void) {
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
+    return major == 10;
+}
+
+// ------------------------------------------------------------------------------------------ prefill
+int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
+    int rc = check_common(p);
+    if (rc) return rc;
+    if ((rc = check_device())) return rc;
+    const bool varlen = p->cu_seqlens_q != nullptr;
+    const bool paged = p->block_table != nullptr;
+    if (varlen && !p->cu_seqlens_k) return fail(MFA_ERR_INVALID_ARG, "cu_seqlens_k must be given with cu_seqlens_q");
+    if (paged && !varlen) return fail(MFA_ERR_INVALID_ARG, "block_table requires the varlen entry (cu_seqlens)");
+    if (p->seqlen_q <= 0) return fail(MFA_ERR_INVALID_ARG, "seqlen_q must be positive");
+    if (!mult8(p->q_row_stride) || !mult8(p->q_head_stride) || !mult8(p->k_row_stride) || !mult8(p->k_head_stride) ||
+        !mult8(p->v_row_stride) || !mult8(p->v_head_stride) || !mult8(p->o_row_stride) || !mult8(p->o_head_stride) ||
+        (!varlen && (!mult8(p->q_batch_stride) || !mult8(p->k_batch_stride) || !mult8(p->v_batch_stride) ||
+                     !mult8(p->o_batch_stride))))
+        return fail(MFA_ERR_UNSUPPORTED, "row/head/batch strides must be multiples of 8 elements (16 bytes)");
+    if (reinterpret_cast<uintptr_t>(p->o_ptr) & 15) return fail(MFA_ERR_UNSUPPORTED, "output must be 16-byte aligned");
+
+    const int D = p->head_dim;
+    const int dpad = dpad_of(D);
+    const bool bf16 = p->is_bf16 != 0;
+
+    CUtensorMap tmQ, tmK, tmV;
+    const char* err;
+    {
+        const uint64_t rows = varlen ? (uint64_t)p->total_q : (uint64_t)p->seqlen_q;
+        if (rows == 0) return fail(MFA_ERR_INVALID_ARG, "q has no rows");
+        const uint64_t dims[4] = {(uint64_t)D, rows, (uint64_t)p->heads, varlen ? 1ull : (uint64_t)p->batch};
+        const int64_t strides[4] = {1, p->q_row_stride, p->q_head_stride, varlen ? 0 : p->q_batch_stride};
+        const uint32_t box[4] = {64, (uint32_t)mfa::kPrefillBlockM, 1, 1};
+        if ((err = mfa::encode_tmap_4d(&tmQ, p->q_ptr, bf16, dims, strides, box))) return fail(MFA_ERR_UNSUPPORTED, "q: %s", err);
+    }
+    int kv_box_rows = mfa::kPrefillBlockN;
+    if (paged) {
+        if (p->page_block_size <= 0 || p->num_blocks <= 0 || p->max_blocks_per_seq <= 0)
+            return fail(MFA_ERR_INVALID_ARG, "paged K/V needs page_block_size, num_blocks and max_blocks_per_seq");
+        kv_box_rows = gcd_int(p->page_block_size, mfa::kPrefillBlockN);
+        if (kv_box_rows < 8)
+            return fail(MFA_ERR_UNSUPPORTED, "page_block_size must be a multiple of 8 (got %d)", p->page_block_size);
+        if (!mult8(p->k_cache_block_stride) || !mult8(p->v_cache_block_stride))
+            return fail(MFA_ERR_UNSUPPORTED, "cache block strides must be multiples of 8 elements");
+        const uint64_t dims[4] = {(uint64_t)D, (uint64_t)p->page_block_size, (uint64_t)p->kv_heads, (uint64_t)p->num_blocks};
+        const int64_t ks[4] = {1, p->k_row_stride, p->k_head_stride, p->k_cache_block_stride};
+        const int64_t vs[4] = {1, p->v_row_stride, p->v_head_stride, p->v_cache_block_stride};
+        const uint32_t box[4] = {64, (uint32_t)kv_box_rows, 1, 1};
+        if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k: %s", err);
+        if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v: %s", err);
+    } else {
+        const uint64_t rows = varlen ? (uint64_t)p->total_k : (uint64_t)p->seqlen_k;
+        if (rows == 0) return fail(MFA_ERR_INVALID_ARG, "k has no rows");
+        const uint64_t dims[4] = {(uint64_t)D, rows, (uint64_t)p->kv_heads, varlen ? 1ull : (uint64_t)p->batch};
+        const int64_t ks[4] = {1, p->k_row_stride, p->k_head_stride, varlen ? 0 : p->k_batch_stride};
+        const int64_t vs[4] = {1, p->v_row_stride, p->v_head_stride, varlen ? 0 : p->v_batch_stride};
+        const uint32_t box[4] = {64, (uint32_t)mfa::kPrefillBlockN, 1, 1};
+        if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k: %s", err);
+        if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v: %s", err);
+    }
+
+    mfa::PrefillKParams kp{};
+    kp.o = p->o_ptr;
+    kp.o_batch_stride = p->o_batch_stride;
+    kp.o_head_stride = p->o_head_stride;
+    kp.o_row_stride = p->o_row_stride;
+    kp.cu_seqlens_q = p->cu_seqlens_q;
+    kp.cu_seqlens_k = p->cu_seqlens_k;
+    kp.block_table = p->block_table;
+    kp.block_table_batch_stride = p->block_table_batch_stride;
+    kp.max_blocks_per_seq = p->max_blocks_per_seq;
+    kp.page = p->page_block_size;
+    kp.kv_box_rows = kv_box_rows;
+    kp.heads = p->heads;
+    kp.kv_heads = p->kv_heads;
+    kp.group = p->heads / p->kv_heads;
+    kp.batch = p->batch;
+    kp.head_dim = D;
+    kp.seqlen_q = p->seqlen_q;
+    kp.seqlen_k = p->seqlen_k;
+    kp.is_causal = p->is_causal ? 1 : 0;
+    const int rows_per_cta = mfa::prefill_rows_per_cta(dpad);
+    kp.num_m_blocks = (p->seqlen_q + rows_per_cta - 1) / rows_per_cta;
+    kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);   // api.cpp:99
+    kp.scale_log2 = kp.scale * 1.4426950408889634f;                                      // api.cpp:100
+    kp.lse = nullptr;
+
+    cudaError_t e = mfa::launch_prefill(tmQ, tmK, tmV, kp, bf16, dpad, static_cast<cudaStream_t>(cuda_stream));
+    if (e != cudaSuccess) return cuda_fail(e, "prefill launch");
+    g_launches.fetch_add(1);
+    return MFA_OK;
+}
+
+// ------------------------------------------------------------------------------------------ decode
+static int decode_splits_for(const mfa_params_t* p) {
+    const int block_n = mfa::kDecodeTileRows;   // api.cpp:314-315
+    const int num_n_blocks = std::max(1, (p->seqlen_k + block_n - 1) / block_n);
+    int splits = p->num_splits;
+    if (splits < 1) {
+        // Heuristic in the spirit of api.cpp:269-302, re-derived for this kernel: one CTA serves a whole GQA
+        // group, two CTAs are resident per SM, and a split should keep >= 4 tiles (256 rows) of work.
+        const int group = p->heads / p->kv_heads;
+        const int head_tiles = (group + mfa::kDecodeMaxGroup - 1) / mfa::kDecodeMaxGroup;
+        const int base = p->batch * p->kv_heads * head_tiles;
+        const int slots = 2 * sm_count();
+        if (base * 10 >= slots * 8) {
+            splits = 1;
+        } else {
+            const int max_splits = std::min({128, std::max(1, num_n_blocks / 4), num_n_blocks});
+            float best_eff = 0.f;
+            int best = 1;
+            for (int s = 1; s <= max_splits; ++s) {
+                const float waves = (float)(base * s) / (float)slots;
+                const float eff = waves / std::ceil(waves);
+                if (eff > best_eff + 1e-6f) {
+                    best_eff = eff;
+                    best = s;
+                }
+                if (eff >= 0.9f && base * s >= slots) break;
+            }
+            splits = best;
+        }
+    }
+    return std::max(1, std::min(splits, num_n_blocks));   // api.cpp:325-327
+}
+
+int mfa_decode_num_splits(const mfa_params_t* p) {
+    if (check_common(p)) return -1;
+    return decode_splits_for(p);
+}
+
+size_t mfa_decode_workspace_bytes(const mfa_params_t* p, int num_splits) {
+    if (!p || num_splits <= 1) return 0;
+    const size_t rows = (size_t)p->batch * (size_t)p->heads;
+    return (size_t)num_splits * rows * ((size_t)p->head_dim + 1) * sizeof(float);   // api.cpp:333-334
+}
+
+int mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    int rc = check_common(p);
+    if (rc) return rc;
+    if ((rc = check_device())) return rc;
+    if (p->seqlen_q != 1) return fail(MFA_ERR_INVALID_ARG, "flash decoding expects seqlen_q == 1, got %d", p->seqlen_q);
+    if (p->seqlen_k <= 0) return fail(MFA_ERR_INVALID_ARG, "KV cache has no rows");
+    const bool paged = p->block_table != nullptr;
+    if (!mult8(p->k_row_stride) || !mult8(p->k_head_stride) || !mult8(p->v_row_stride) || !mult8(p->v_head_stride))
+        return fail(MFA_ERR_UNSUPPORTED, "cache row/head strides must be multiples of 8 elements (16 bytes)");
+    if ((p->q_head_stride % 2) || (p->q_batch_stride % 2) || (reinterpret_cast<uintptr_t>(p->q_ptr) & 3))
+        return fail(MFA_ERR_UNSUPPORTED, "q strides must be even and q 4-byte aligned");
+    if (p->partial_out) {
+        if (!p->softmax_lse_ptr) return fail(MFA_ERR_INVALID_ARG, "partial_out requires softmax_lse_ptr");
+        if (reinterpret_cast<uintptr_t>(p->o_ptr) & 15) return fail(MFA_ERR_UNSUPPORTED, "partial output must be 16-byte aligned");
+    } else if ((p->o_head_stride % 4) || (p->o_batch_stride % 4) || (reinterpret_cast<uintptr_t>(p->o_ptr) & 7)) {
+        return fail(MFA_ERR_UNSUPPORTED, "output strides must be multiples of 4 elements and 8-byte aligned");
+    }
+
+    const int D = p->head_dim;
+    const int dpad = dpad_of(D);
+    const bool bf16 = p->is_bf16 != 0;
+    const int splits = decode_splits_for(p);
+    const size_t need = mfa_decode_workspace_bytes(p, splits);
+    if (need > 0 && (!workspace || workspace_bytes < need))
+        return fail(MFA_ERR_INVALID_ARG, "decode workspace too small: need %zu bytes for %d splits, got %zu", need, splits,
+                    workspace_bytes);
+    if (need > 0 && (reinterpret_cast<uintptr_t>(workspace) & 15)) return fail(MFA_ERR_UNSUPPORTED, "workspace must be 16-byte aligned");
+
+    CUtensorMap tmK, tmV;
+    const char* err;
+    int box_rows = mfa::kDecodeTileRows;
+    int page = p->seqlen_k;
+    if (paged) {
+        if (p->page_block_size <= 0 || p->num_blocks <= 0 || p->max_blocks_per_seq <= 0)
+            return fail(MFA_ERR_INVALID_ARG, "paged cache needs page_block_size, num_blocks and max_blocks_per_seq");
+        page = p->page_block_size;
+        box_rows = gcd_int(page, mfa::kDecodeTileRows);
+        if (box_rows < 8) return fail(MFA_ERR_UNSUPPORTED, "page_block_size must be a multiple of 8 (got %d)", page);
+        if (!mult8(p->k_cache_block_stride) || !mult8(p->v_cache_block_stride))
+            return fail(MFA_ERR_UNSUPPORTED, "cache block strides must be multiples of 8 elements");
+        const uint64_t dims[4] = {(uint64_t)D, (uint64_t)page, (uint64_t)p->kv_heads, (uint64_t)p->num_blocks};
+        const int64_t ks[4] = {1, p->k_row_stride, p->k_head_stride, p->k_cache_block_stride};
+        const int64_t vs[4] = {1, p->v_row_stride, p->v_head_stride, p->v_cache_block_stride};
+        const uint32_t box[4] = {64, (uint32_t)box_rows, 1, 1};
+        if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k_cache: %s", err);
+        if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v_cache: %s", err);
+    } else {
+        if (!mult8(p->k_batch_stride) || !mult8(p->v_batch_stride))
+            return fail(MFA_ERR_UNSUPPORTED, "cache batch strides must be multiples of 8 elements");
+        const uint64_t dims[4] = {(uint64_t)D, (uint64_t)p->seqlen_k, (uint64_t)p->kv_heads, (uint64_t)p->batch};
+        const int64_t ks[4] = {1, p->k_row_stride, p->k_head_stride, p->k_batch_stride};
+        const int64_t vs[4] = {1, p->v_row_stride, p->v_head_stride, p->v_batch_stride};
+        const uint32_t box[4] = {64, (uint32_t)box_rows, 1, 1};
+        if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k_cache: %s", err);
+        if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v_cache: %s", err);
+    }
+
+    const size_t rows = (size_t)p->batch * (size_t)p->heads;
+    mfa::DecodeKParams kp{};
+    kp.q = p->q_ptr;
+    kp.o = p->o_ptr;
+    kp.lse = p->softmax_lse_ptr;
+    kp.o_part = splits > 1 ? static_cast<float*>(workspace) : nullptr;
+    kp.lse_part = splits > 1 ? static_cast<float*>(workspace) + (size_t)splits * rows * D : nullptr;
+    kp.q_batch_stride = p->q_batch_stride;
+    kp.q_head_stride = p->q_head_stride;
+    kp.o_batch_stride = p->o_batch_stride;
+    kp.o_head_stride = p->o_head_stride;
+    kp.seqlens_k = p->seqlens_k;
+    kp.block_table = p->block_table;
+    kp.block_table_batch_stride = p->block_table_batch_stride;
+    kp.max_blocks_per_seq = p->max_blocks_per_seq;
+    kp.page = page;
+    kp.box_rows = box_rows;
+    kp.heads = p->heads;
+    kp.kv_heads = p->kv_heads;
+    kp.group = p->heads / p->kv_heads;
+    kp.batch = p->batch;
+    kp.head_dim = D;
+    kp.seqlen_k = p->seqlen_k;
+    kp.num_splits = splits;
+    kp.head_tiles = (kp.group + mfa::kDecodeMaxGroup - 1) / mfa::kDecodeMaxGroup;
+    kp.partial_out = p->partial_out ? 1 : 0;
+    kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);
+    kp.scale_log2 = kp.scale * 1.4426950408889634f;
+
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    cudaError_t e = mfa::launch_decode(tmK, tmV, kp, bf16, dpad, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "decode launch");
+    g_launches.fetch_add(1);
+    if (splits > 1) {
+        mfa::CombineKParams cp{};
+        cp.out_f32 = p->partial_out ? 1 : 0;   // KV-sharded decode: the merged result stays a normalised fp32 partial
+        cp.o_part = kp.o_part;
+        cp.lse_part = kp.lse_part;
+        cp.out = p->o_ptr;
+        cp.lse_out = p->softmax_lse_ptr;
+        cp.out_batch_stride = p->partial_out ? (int64_t)p->heads * D : p->o_batch_stride;
+        cp.out_head_stride = p->partial_out ? (int64_t)D : p->o_head_stride;
+        cp.heads = p->heads;
+        cp.num_splits = splits;
+        cp.rows = (int)rows;
+        cp.head_dim = D;
+        cp.packed = 0;
+        e = mfa::launch_combine(cp, bf16, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "combine launch");
+        g_launches.fetch_add(1);
+    }
+    return MFA_OK;
+}
+
+int mfa_combine_partials(const float* packed, int num_partials, int rows, int head_dim, void* out,
+                         int64_t out_row_stride, int is_bf16, float* lse_out, void* cuda_stream) {
+    if (!packed || !out || num_partials <= 0 || rows <= 0 || head_dim <= 0 || head_dim % 4)
+        return fail(MFA_ERR_INVALID_ARG, "combine: bad arguments");
+    if ((out_row_stride % 4) || (reinterpret_cast<uintptr_t>(out) & 7))
+        return fail(MFA_ERR_UNSUPPORTED, "combine: output rows must be 8-byte aligned");
+    int rc = check_device();
+    if (rc) return rc;
+    mfa::CombineKParams cp{};
+    cp.o_part = packed;
+    cp.lse_part = nullptr;
+    cp.out = out;
+    cp.lse_out = lse_out;
+    cp.out_row_stride = out_row_stride;
+    cp.heads = 0;
+    cp.num_splits = num_partials;
+    cp.rows = rows;
+    cp.head_dim = head_dim;
+    cp.packed = 1;
+    cudaError_t e = mfa::launch_combine(cp, is_bf16 != 0, static_cast<cudaStream_t>(cuda_stream));
+    if (e != cudaSuccess) return cuda_fail(e, "combine launch");
+    g_launches.fetch_add(1);
+    return MFA_OK;
+}
+
+}  // extern "C"

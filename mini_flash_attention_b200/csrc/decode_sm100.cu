@@ -1,0 +1,493 @@
+// decode_sm100.cu -- q_len == 1 split-KV attention ("flash decoding") for sm_100a, plus the LSE combine.
+//
+// Replaces /root/reference/csrc/mfa/decode.cuh:523-662 (split-KV kernel) and :665-755 (combine).
+// Not a port: the reference runs one CTA per *query* head with single-buffered cp.async tiles and
+// CUDA-core dot products with a 5-step shuffle reduction per key row; here
+//   * one CTA owns (batch, KV head, split) and serves the whole GQA group, so K/V are read from HBM
+//     exactly once per KV head (the reference re-reads them `group` times, decode.cuh:48);
+//   * a dedicated producer warp streams 64-row K and V tiles with TMA (cp.async.bulk.tensor, 128B
+//     swizzle, per-page boxes gathered through block_table) into a multi-stage mbarrier ring, so
+//     ~100 KB per CTA are in flight independent of the consumers' registers;
+//   * four consumer warps each take 16 rows of a tile: S = Q K^T and O += P V run on the tensor cores
+//     (mma.sync m16n8k16, the q heads of the group padded to M = 16), operands fetched with
+//     ldmatrix from the swizzled tiles (conflict-free), online softmax in the exp2 domain in fp32;
+//   * the four per-warp partial (max, sum, O) states are merged through shared memory, and the CTA
+//     writes either the final output (1 split) or a normalised fp32 partial + LSE for the combine.
+// The split partition is the reference's (decode.cuh:21-30): blocks of 64 rows,
+// blocks_per_split = ceil(ceil(len/64)/num_splits); empty splits write LSE = -inf.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "kparams.h"
+#include "ptx.cuh"
+
+namespace mfa {
+
+namespace {
+
+template <typename T>
+struct Pack2;
+template <>
+struct Pack2<__half> {
+    static __device__ __forceinline__ uint32_t pack(float a, float b) {
+        __half2 h = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+    static __device__ __forceinline__ void store(__half* p, float v) { *p = __float2half_rn(v); }
+};
+template <>
+struct Pack2<__nv_bfloat16> {
+    static __device__ __forceinline__ uint32_t pack(float a, float b) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+    static __device__ __forceinline__ void store(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+};
+
+template <typename T>
+__device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
+template <>
+__device__ __forceinline__ void mma_16816<__half>(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <>
+__device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                                          uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(addr));
+}
+
+// Byte offset of 16-byte chunk `chunk` (0 .. DPAD/8) of row `row` inside a [DPAD/64][64 rows][128 B] tile
+// written by TMA with CU_TENSOR_MAP_SWIZZLE_128B (tile base 1024-byte aligned).
+template <int ROWS>
+__device__ __forceinline__ uint32_t swz_off(int row, int chunk) {
+    return static_cast<uint32_t>((chunk >> 3) * (ROWS * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4));
+}
+
+template <int DPAD>
+struct DecodeCfg {
+    static constexpr int kTile = kDecodeTileRows;
+    static constexpr int kTileBytes = kTile * DPAD * 2;          // one of K or V
+    static constexpr int kStageBytes = 2 * kTileBytes;           // K then V
+    static constexpr int kStages = (DPAD == 64) ? 6 : 3;
+    static constexpr int kRingBytes = kStages * kStageBytes;
+    static constexpr int kSmemBytes = kRingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <typename T, int DPAD>
+__global__ void __launch_bounds__(kDecodeThreads) decode_splitkv_kernel(const __grid_constant__ CUtensorMap tmK,
+                                                                        const __grid_constant__ CUtensorMap tmV,
+                                                                        const __grid_constant__ DecodeKParams p) {
+    using Cfg = DecodeCfg<DPAD>;
+    constexpr int kTile = Cfg::kTile;
+    constexpr int kStages = Cfg::kStages;
+    constexpr int KS = DPAD / 16;   // k-steps of QK^T
+    constexpr int NT = DPAD / 8;    // n-tiles of PV
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kRingBytes);
+    uint64_t* empty_bar = full_bar + kStages;
+
+    const int split = blockIdx.x;
+    const int kh = blockIdx.y / p.head_tiles;
+    const int htile = blockIdx.y % p.head_tiles;
+    const int b = blockIdx.z;
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const int len = p.seqlens_k ? min(p.seqlens_k[b], p.seqlen_k) : p.seqlen_k;
+    const int n_blocks = (len + kTile - 1) / kTile;
+    const int per_split = (n_blocks + p.num_splits - 1) / p.num_splits;   // decode.cuh:27
+    const int t0 = split * per_split;
+    const int t1 = min(n_blocks, t0 + per_split);
+    const int ntiles = max(t1 - t0, 0);
+
+    const int gvalid = min(p.group - htile * kDecodeMaxGroup, kDecodeMaxGroup);   // q heads served by this CTA
+    const int head0 = kh * p.group + htile * kDecodeMaxGroup;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 4);
+        }
+        fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == 4) {
+        // ------------------------------------------------------------ TMA producer
+        if (lane == 0 && ntiles > 0) {
+            prefetch_tensormap(&tmK);
+            prefetch_tensormap(&tmV);
+            const int32_t* bt = p.block_table ? p.block_table + (int64_t)b * p.block_table_batch_stride : nullptr;
+            const int chunk_bytes = p.box_rows * 128;   // one box = box_rows x 64 elements
+            for (int it = 0; it < ntiles; ++it) {
+                const int s = it % kStages;
+                const uint32_t ph = (it / kStages) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                const int row0 = (t0 + it) * kTile;
+                const int rows_valid = min(len - row0, kTile);
+                const int nchunks = (rows_valid + p.box_rows - 1) / p.box_rows;
+                mbar_arrive_expect_tx(&full_bar[s], static_cast<uint32_t>(nchunks * chunk_bytes * (DPAD / 64) * 2));
+                uint8_t* kdst = smem + s * Cfg::kStageBytes;
+                uint8_t* vdst = kdst + Cfg::kTileBytes;
+                for (int c = 0; c < nchunks; ++c) {
+                    const int row = row0 + c * p.box_rows;
+                    int blk, in_page;
+                    if (bt) {
+                        const int pg = row / p.page;
+                        in_page = row - pg * p.page;
+                        blk = bt[pg];
+                    } else {
+                        in_page = row;
+                        blk = b;
+                    }
+#pragma unroll
+                    for (int hf = 0; hf < DPAD / 64; ++hf) {
+                        tma_load_4d(kdst + hf * (kTile * 128) + c * chunk_bytes, &tmK, &full_bar[s], hf * 64, in_page, kh,
+                                    blk);
+                        tma_load_4d(vdst + hf * (kTile * 128) + c * chunk_bytes, &tmV, &full_bar[s], hf * 64, in_page, kh,
+                                    blk);
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ---------------------------------------------------------------- consumers (warps 0..3)
+    const T* qbase = static_cast<const T*>(p.q) + (int64_t)b * p.q_batch_stride;
+    const int g0 = lane >> 2;        // head row of c0,c1 / a0,a2
+    const int g1 = g0 + 8;           // head row of c2,c3 / a1,a3
+    const int tq = lane & 3;
+
+    uint32_t qa[KS][4];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+        const int c = ks * 16 + tq * 2;
+        const T* q0 = qbase + (int64_t)(head0 + g0) * p.q_head_stride;
+        const T* q1 = qbase + (int64_t)(head0 + g1) * p.q_head_stride;
+        qa[ks][0] = (g0 < gvalid && c < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q0 + c) : 0u;
+        qa[ks][1] = (g1 < gvalid && c < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q1 + c) : 0u;
+        qa[ks][2] = (g0 < gvalid && c + 8 < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q0 + c + 8) : 0u;
+        qa[ks][3] = (g1 < gvalid && c + 8 < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q1 + c + 8) : 0u;
+    }
+
+    float o[NT][4];
+#pragma unroll
+    for (int i = 0; i < NT; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    const float c2 = p.scale_log2;
+    const int wrow = warp * 16;   // this warp's rows inside each tile
+
+    for (int it = 0; it < ntiles; ++it) {
+        const int s = it % kStages;
+        const uint32_t ph = (it / kStages) & 1;
+        mbar_wait(&full_bar[s], ph);
+        const uint32_t kaddr = smem_u32(smem + s * Cfg::kStageBytes);
+        const uint32_t vaddr = kaddr + Cfg::kTileBytes;
+        const int row0 = (t0 + it) * kTile;
+        const int rows_valid = len - row0;   // >= 1
+
+        if (rows_valid < wrow + 16) {
+            // tail tile: rows >= len hold stale cache bytes (possibly NaN); zero this warp's V rows so that
+            // P(=0) * V stays 0 (the reference zero-fills them with cp.async zfill, decode.cuh:243-249).
+            uint8_t* vt = smem + s * Cfg::kStageBytes + Cfg::kTileBytes;
+            for (int r = max(rows_valid - wrow, 0); r < 16; ++r) {
+                const int row = wrow + r;
+#pragma unroll
+                for (int hf = 0; hf < DPAD / 64; ++hf)
+                    *reinterpret_cast<uint32_t*>(vt + hf * (kTile * 128) + row * 128 + lane * 4) = 0u;
+            }
+            fence_proxy_async_smem();   // generic writes ordered before the next TMA refill of this stage
+            __syncwarp();
+        }
+
+        // ---- S = Q K^T for this warp's 16 KV rows
+        float sc[2][4];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) sc[i][0] = sc[i][1] = sc[i][2] = sc[i][3] = 0.f;
+        {
+            const int mi = lane >> 3, r = lane & 7;
+            const int row = wrow + (mi >> 1) * 8 + r;
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks) {
+                uint32_t kb[4];
+                ldsm_x4(kb, kaddr + swz_off<kTile>(row, 2 * ks + (mi & 1)));
+                mma_16816<T>(sc[0], qa[ks], kb[0], kb[1]);
+                mma_16816<T>(sc[1], qa[ks], kb[2], kb[3]);
+            }
+        }
+        // ---- tail mask (decode.cuh:327-336)
+        if (rows_valid < wrow + 16) {
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+                const int kv = wrow + nt * 8 + tq * 2;
+                if (kv >= rows_valid) sc[nt][0] = sc[nt][2] = -INFINITY;
+                if (kv + 1 >= rows_valid) sc[nt][1] = sc[nt][3] = -INFINITY;
+            }
+        }
+        // ---- online softmax (exp2 domain), two head rows per thread
+        float tm0 = fmaxf(fmaxf(sc[0][0], sc[0][1]), fmaxf(sc[1][0], sc[1][1]));
+        float tm1 = fmaxf(fmaxf(sc[0][2], sc[0][3]), fmaxf(sc[1][2], sc[1][3]));
+        tm0 = fmaxf(tm0, __shfl_xor_sync(0xffffffffu, tm0, 1));
+        tm0 = fmaxf(tm0, __shfl_xor_sync(0xffffffffu, tm0, 2));
+        tm1 = fmaxf(tm1, __shfl_xor_sync(0xffffffffu, tm1, 1));
+        tm1 = fmaxf(tm1, __shfl_xor_sync(0xffffffffu, tm1, 2));
+        const float mn0 = fmaxf(m0, tm0), mn1 = fmaxf(m1, tm1);
+        const float r0 = (mn0 == -INFINITY) ? 1.f : exp2f((m0 - mn0) * c2);
+        const float r1 = (mn1 == -INFINITY) ? 1.f : exp2f((m1 - mn1) * c2);
+        const float ms0 = (mn0 == -INFINITY) ? 0.f : mn0 * c2;
+        const float ms1 = (mn1 == -INFINITY) ? 0.f : mn1 * c2;
+        m0 = mn0;
+        m1 = mn1;
+        float ps0 = 0.f, ps1 = 0.f;
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+            sc[nt][0] = exp2f(sc[nt][0] * c2 - ms0);
+            sc[nt][1] = exp2f(sc[nt][1] * c2 - ms0);
+            sc[nt][2] = exp2f(sc[nt][2] * c2 - ms1);
+            sc[nt][3] = exp2f(sc[nt][3] * c2 - ms1);
+            ps0 += sc[nt][0] + sc[nt][1];
+            ps1 += sc[nt][2] + sc[nt][3];
+        }
+        l0 = l0 * r0 + ps0;
+        l1 = l1 * r1 + ps1;
+        if (__any_sync(0xffffffffu, (r0 != 1.f) || (r1 != 1.f))) {
+#pragma unroll
+            for (int i = 0; i < NT; ++i) {
+                o[i][0] *= r0;
+                o[i][1] *= r0;
+                o[i][2] *= r1;
+                o[i][3] *= r1;
+            }
+        }
+        // ---- O += P V
+        uint32_t pa[4];
+        pa[0] = Pack2<T>::pack(sc[0][0], sc[0][1]);
+        pa[1] = Pack2<T>::pack(sc[0][2], sc[0][3]);
+        pa[2] = Pack2<T>::pack(sc[1][0], sc[1][1]);
+        pa[3] = Pack2<T>::pack(sc[1][2], sc[1][3]);
+        {
+            const int mi = lane >> 3, r = lane & 7;
+            const int row = wrow + (mi & 1) * 8 + r;
+#pragma unroll
+            for (int n2 = 0; n2 < NT / 2; ++n2) {
+                uint32_t vb[4];
+                ldsm_x4_trans(vb, vaddr + swz_off<kTile>(row, 2 * n2 + (mi >> 1)));
+                mma_16816<T>(o[2 * n2], pa, vb[0], vb[1]);
+                mma_16816<T>(o[2 * n2 + 1], pa, vb[2], vb[3]);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[s]);
+    }
+
+    // ---------------------------------------------------------------- cross-warp merge
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+
+    named_bar_sync(1, 128);   // every consumer is done reading the ring; all issued TMA has landed
+    float* stage_o = reinterpret_cast<float*>(smem);                    // [4 warps][16 heads][DPAD]
+    float* stage_m = reinterpret_cast<float*>(smem + 4 * 16 * DPAD * 4);  // [4][16]
+    float* stage_l = stage_m + 64;
+    if (tq == 0) {
+        stage_m[warp * 16 + g0] = m0;
+        stage_m[warp * 16 + g1] = m1;
+        stage_l[warp * 16 + g0] = l0;
+        stage_l[warp * 16 + g1] = l1;
+    }
+#pragma unroll
+    for (int i = 0; i < NT; ++i) {
+        const int col = i * 8 + tq * 2;
+        float* w0 = stage_o + (warp * 16 + g0) * DPAD + col;
+        float* w1 = stage_o + (warp * 16 + g1) * DPAD + col;
+        *reinterpret_cast<float2*>(w0) = make_float2(o[i][0], o[i][1]);
+        *reinterpret_cast<float2*>(w1) = make_float2(o[i][2], o[i][3]);
+    }
+    named_bar_sync(1, 128);
+
+    const bool write_partial = (p.num_splits > 1);
+    for (int idx = threadIdx.x; idx < gvalid * (DPAD / 4); idx += 128) {
+        const int hr = idx / (DPAD / 4);
+        const int col = (idx % (DPAD / 4)) * 4;
+        float mw[4], mx = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            mw[w] = stage_m[w * 16 + hr];
+            mx = fmaxf(mx, mw[w]);
+        }
+        float L = 0.f, wgt[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            wgt[w] = (mw[w] == -INFINITY) ? 0.f : exp2f((mw[w] - mx) * c2);
+            L += stage_l[w * 16 + hr] * wgt[w];
+        }
+        const float inv = (L > 0.f) ? 1.f / L : 0.f;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const float4 v = *reinterpret_cast<const float4*>(stage_o + (w * 16 + hr) * DPAD + col);
+            acc.x += v.x * wgt[w];
+            acc.y += v.y * wgt[w];
+            acc.z += v.z * wgt[w];
+            acc.w += v.w * wgt[w];
+        }
+        acc.x *= inv;
+        acc.y *= inv;
+        acc.z *= inv;
+        acc.w *= inv;
+        const int head = head0 + hr;
+        const float lse = (L > 0.f) ? mx * p.scale + __logf(L) : -INFINITY;   // decode.cuh:649
+        if (col < p.head_dim) {
+            if (write_partial) {
+                float* dst = p.o_part + (((int64_t)split * p.batch + b) * p.heads + head) * p.head_dim + col;
+                *reinterpret_cast<float4*>(dst) = acc;
+            } else if (p.partial_out) {
+                float* dst = static_cast<float*>(p.o) + ((int64_t)b * p.heads + head) * p.head_dim + col;
+                *reinterpret_cast<float4*>(dst) = acc;
+            } else {
+                T* dst = static_cast<T*>(p.o) + (int64_t)b * p.o_batch_stride + (int64_t)head * p.o_head_stride + col;
+                uint2 pk;
+                pk.x = Pack2<T>::pack(acc.x, acc.y);
+                pk.y = Pack2<T>::pack(acc.z, acc.w);
+                *reinterpret_cast<uint2*>(dst) = pk;
+            }
+        }
+        if (col == 0) {
+            if (write_partial) {
+                p.lse_part[((int64_t)split * p.batch + b) * p.heads + head] = lse;
+            } else if (p.lse) {
+                p.lse[(int64_t)b * p.heads + head] = lse;
+            }
+        }
+    }
+}
+
+// LSE merge of `num_splits` normalised partials (decode.cuh:665-755 restated with a max-subtracted
+// log-sum-exp and no shared memory proportional to the split count).
+// One warp per output row (b, h); lanes stride over head_dim in float4.
+template <typename T>
+__global__ void __launch_bounds__(128) combine_kernel(const __grid_constant__ CombineKParams p) {
+    const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= p.rows) return;
+    const int D = p.head_dim;
+    const int pstride = p.packed ? (D + 1) : D;
+    auto lse_of = [&](int s) -> float {
+        return p.packed ? p.o_part[((int64_t)s * p.rows + row) * pstride + D]
+                        : p.lse_part[(int64_t)s * p.rows + row];
+    };
+    float mx = -INFINITY;
+    for (int s = lane; s < p.num_splits; s += 32) mx = fmaxf(mx, lse_of(s));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float tot = 0.f;
+    for (int s = lane; s < p.num_splits; s += 32) {
+        const float l = lse_of(s);
+        tot += (l == -INFINITY) ? 0.f : __expf(l - mx);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    const float glse = (mx == -INFINITY) ? -INFINITY : mx + __logf(tot);
+
+    const int64_t out_off = (p.heads > 0) ? (int64_t)(row / p.heads) * p.out_batch_stride +
+                                                (int64_t)(row % p.heads) * p.out_head_stride
+                                          : (int64_t)row * p.out_row_stride;
+    T* out = static_cast<T*>(p.out) + out_off;
+    float* out32 = static_cast<float*>(p.out) + out_off;
+    for (int col = lane * 4; col < D; col += 128) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int s = 0; s < p.num_splits; ++s) {
+            const float l = lse_of(s);
+            if (l == -INFINITY) continue;
+            const float w = __expf(l - glse);
+            const float* src = p.o_part + ((int64_t)s * p.rows + row) * pstride + col;
+            float4 v;
+            if (p.packed) {   // rows of D+1 floats are not 16-byte aligned
+                v = make_float4(src[0], src[1], src[2], src[3]);
+            } else {
+                v = *reinterpret_cast<const float4*>(src);
+            }
+            acc.x += v.x * w;
+            acc.y += v.y * w;
+            acc.z += v.z * w;
+            acc.w += v.w * w;
+        }
+        if (p.out_f32) {
+            *reinterpret_cast<float4*>(out32 + col) = acc;
+        } else {
+            uint2 pk;
+            pk.x = Pack2<T>::pack(acc.x, acc.y);
+            pk.y = Pack2<T>::pack(acc.z, acc.w);
+            *reinterpret_cast<uint2*>(out + col) = pk;
+        }
+    }
+    if (lane == 0 && p.lse_out) p.lse_out[row] = glse;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------- launchers
+template <typename T, int DPAD>
+static cudaError_t launch_decode_t(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeKParams& p,
+                                   cudaStream_t stream) {
+    using Cfg = DecodeCfg<DPAD>;
+    auto kern = decode_splitkv_kernel<T, DPAD>;
+    static bool attr_done[64] = {};   // per (T, DPAD) instantiation and device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && !attr_done[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        if (e != cudaSuccess) return e;
+        attr_done[dev] = true;
+    }
+    dim3 grid(p.num_splits, p.kv_heads * p.head_tiles, p.batch);
+    kern<<<grid, kDecodeThreads, Cfg::kSmemBytes, stream>>>(tmK, tmV, p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeKParams& p, bool is_bf16,
+                          int dpad, cudaStream_t stream) {
+#define MFA_DECODE_CASE(DP)                                                                  \
+    case DP:                                                                                 \
+        return is_bf16 ? launch_decode_t<__nv_bfloat16, DP>(tmK, tmV, p, stream)             \
+                       : launch_decode_t<__half, DP>(tmK, tmV, p, stream);
+    switch (dpad) {
+        MFA_DECODE_CASE(64)
+        MFA_DECODE_CASE(128)
+        MFA_DECODE_CASE(256)
+        default:
+            return cudaErrorInvalidValue;
+    }
+#undef MFA_DECODE_CASE
+}
+
+cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream) {
+    dim3 grid((p.rows + 3) / 4);
+    if (is_bf16)
+        combine_kernel<__nv_bfloat16><<<grid, 128, 0, stream>>>(p);
+    else
+        combine_kernel<__half><<<grid, 128, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace mfa

@@ -1,0 +1,69 @@
+// kparams.h -- kernel-side parameter blocks (internal; the public POD is include/mfa_b200.h).
+#pragma once
+#include <cstdint>
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+namespace mfa {
+
+constexpr int kDecodeTileRows = 64;   // KV rows per pipeline stage == the reference's kBlockN (traits.h, flash.cu:89)
+constexpr int kDecodeThreads = 160;   // 4 consumer warps + 1 TMA producer warp
+constexpr int kDecodeMaxGroup = 16;   // q heads per CTA (one m16 MMA tile)
+
+struct DecodeKParams {
+    const void* q;             // (B, 1, Hq, D)
+    void* o;                   // final output (out dtype), or fp32 when partial_out
+    float* lse;                // optional (B, Hq)
+    float* o_part;             // (splits, B, Hq, D) fp32 when splits > 1
+    float* lse_part;           // (splits, B, Hq)
+    int64_t q_batch_stride, q_head_stride;
+    int64_t o_batch_stride, o_head_stride;
+    const int32_t* seqlens_k;  // may be null -> seqlen_k
+    const int32_t* block_table;  // may be null -> contiguous cache, block index == batch index
+    int32_t block_table_batch_stride;
+    int32_t max_blocks_per_seq;
+    int32_t page;              // rows per page (contiguous cache: capacity rows)
+    int32_t box_rows;          // rows per TMA box (divides 64 and the page size when paged)
+    int32_t heads, kv_heads, group, batch, head_dim;
+    int32_t seqlen_k;          // capacity
+    int32_t num_splits;
+    int32_t head_tiles;        // ceil(group / 16)
+    int32_t partial_out;
+    float scale, scale_log2;
+};
+
+struct CombineKParams {
+    const float* o_part;       // (splits, rows, D) or packed (splits, rows, D+1) when packed != 0
+    const float* lse_part;     // (splits, rows) (unused when packed)
+    void* out;                 // (rows, D) out dtype, row stride out_row_stride
+    float* lse_out;            // optional (rows)
+    int64_t out_row_stride;    // elements; rows are (b*H + h) => caller guarantees uniform stride
+    int64_t out_batch_stride, out_head_stride;  // used when heads > 0 (row = b*heads + h)
+    int32_t heads;
+    int32_t num_splits, rows, head_dim, packed;
+    int32_t out_f32;           // write fp32 instead of the 16-bit dtype (partials of a KV-sharded decode)
+};
+
+constexpr int kPrefillBlockM = 128;   // query rows per Q tile (one TMEM lane per row)
+constexpr int kPrefillBlockN = 128;   // KV rows per tile
+constexpr int kPrefillThreads = 384;  // 2 softmax warpgroups + 1 warpgroup {TMA warp, MMA warp, 2 spare}
+
+struct PrefillKParams {
+    void* o;
+    int64_t o_batch_stride, o_head_stride, o_row_stride;
+    const int32_t* cu_seqlens_q;   // null => fixed length
+    const int32_t* cu_seqlens_k;
+    const int32_t* block_table;    // null => not paged
+    int32_t block_table_batch_stride;
+    int32_t max_blocks_per_seq;
+    int32_t page;                  // rows per page when paged
+    int32_t kv_box_rows;           // rows per K/V TMA box (128, or gcd(page,128) when paged)
+    int32_t heads, kv_heads, group, batch, head_dim;
+    int32_t seqlen_q, seqlen_k;    // fixed lengths or max lengths
+    int32_t is_causal;
+    int32_t num_m_blocks;          // ceil(seqlen_q / 256)
+    float scale, scale_log2;
+    float* lse;                    // optional (B, H, Sq) / (H, total_q): not exposed yet
+};
+
+}  // namespace mfa

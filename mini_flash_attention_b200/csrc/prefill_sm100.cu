@@ -1,0 +1,475 @@
+// prefill_sm100.cu -- FlashAttention forward (prefill) for sm_100a: TMA + mbarrier ring + tcgen05.mma with
+// accumulators in tensor memory + exp2 online softmax with one thread per query row.
+//
+// Replaces /root/reference/csrc/mfa/prefill.cuh:711-803 (kernel) and flash.cu:11-34 (launch).  It is not
+// a port of that sm_80 mma.sync/cp.async kernel (64x64 tiles, 4 warps, single-buffered K/V); the
+// structure here is
+//
+//   CTA = (256 query rows = two 128-row Q tiles, one head, one sequence), 384 threads, 1 CTA / SM
+//   warps 0-3   softmax warpgroup of Q tile 0   (thread t <-> query row t <-> TMEM lane t)
+//   warps 4-7   softmax warpgroup of Q tile 1
+//   warp  8     TMA producer: Q tiles once, then K_0,V_0,K_1,V_1,... through a kStages-deep smem ring
+//   warp  9     MMA issuer (one thread): S_i = Q_i K_j^T (SS) and O_i += P_i V_j (TS, P read from TMEM)
+//   warp 10     TMEM allocator / deallocator
+//
+//   TMEM (512 columns x 128 lanes x 32 bit):  S_0 [0,128)  S_1 [128,256)  O_0 [256,256+D)  O_1 [256+D, 256+2D)
+//   P_i (fp16/bf16, 64 columns) aliases the first half of S_i: a softmax thread has its whole S row in
+//   registers before it overwrites it, and tcgen05.mma instructions execute in issue order, so
+//   S_i(j+1) is only written after PV_i(j) has consumed P_i(j).
+//
+// The two Q tiles ping-pong on the tensor pipe: while warpgroup 0 runs the softmax of tile j, the MMA
+// warp computes PV_1(j-1) and S_1(j) and vice versa.  O stays in TMEM for the whole KV loop; the
+// rescale O *= 2^(m_old-m_new) is done lazily by the owning softmax thread only when the running max
+// grew by more than 2^8 (the final normalisation uses the same stale max for the row sum, so the
+// result is unchanged).
+//
+// Semantics kept from the reference: scale = 1/sqrt(D) folded into exp2 (api.cpp:99-100); causal mask
+// top-left aligned, key col masked iff col > row (prefill.cuh:416) with tile skipping (:749-752);
+// key-length mask col >= len (:416); rows with an empty sum produce 0 (:604-605); GQA
+// kv_head = head / group (:49); varlen through cu_seqlens (:19-33); paged K/V through block_table --
+// gathered per page box, not per 64-row tile (fixes quirk Q3 of SURVEY.md).
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "kparams.h"
+#include "ptx.cuh"
+
+namespace mfa {
+
+namespace {
+
+template <typename T>
+struct Elem;
+template <>
+struct Elem<__half> {
+    static constexpr uint32_t kFmt = 0;
+    static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
+        __half2 h = __floats2half2_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+};
+template <>
+struct Elem<__nv_bfloat16> {
+    static constexpr uint32_t kFmt = 1;
+    static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+};
+
+template <int DPAD>
+struct PrefillCfg {
+    static constexpr int kBM = kPrefillBlockM;
+    static constexpr int kBN = kPrefillBlockN;
+    static constexpr int kNQ = (DPAD <= 128) ? 2 : 1;            // Q tiles per CTA (TMEM budget)
+    static constexpr int kSub = DPAD / 64;                       // 64-column (128-byte) sub-tiles per row
+    static constexpr int kSubBytes = 128 * 128;                  // 128 rows x 128 B
+    static constexpr int kQTileBytes = kSub * kSubBytes;
+    static constexpr int kKVTileBytes = kSub * kSubBytes;
+    static constexpr int kStages = (DPAD == 64) ? 8 : (DPAD == 128 ? 4 : 2);
+    static constexpr int kQBytes = kNQ * kQTileBytes;
+    static constexpr int kRingBytes = kStages * kKVTileBytes;
+    static constexpr int kBarOffset = kQBytes + kRingBytes;
+    static constexpr int kSmemBytes = kBarOffset + 512 + 1024;   // barriers + alignment slack
+    static constexpr uint32_t kTmemCols = 512;
+    static constexpr uint32_t kTmemS = 0;                        // S_i at kTmemS + i*128
+    static constexpr uint32_t kTmemO = 256;                      // O_i at kTmemO + i*DPAD
+    static constexpr float kRescaleThreshold = 8.0f;             // log2 domain
+};
+
+// smem descriptors -------------------------------------------------------------------------------
+// K-major operand (Q or K tile): [sub][128 rows][64 elems], SWIZZLE_128B.  One UMMA K-step = 16 elems = 32 B.
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_addr, int kstep) {
+    const uint32_t addr = tile_addr + (kstep >> 2) * (128 * 128) + (kstep & 3) * 32;
+    return umma_smem_desc(addr, /*LBO*/ 16, /*SBO: 8 rows x 128 B*/ 1024, /*SW128*/ 2);
+}
+// MN-major operand (V tile as B of P.V): [sub(d)][128 kv rows][64 elems(d)], SWIZZLE_128B.
+// One UMMA K-step = 16 kv rows = 2048 B; LBO = distance between 64-wide d sub-tiles, SBO = 8 rows.
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep) {
+    const uint32_t addr = tile_addr + kstep * (16 * 128);
+    return umma_smem_desc(addr, /*LBO*/ 128 * 128, /*SBO*/ 1024, /*SW128*/ 2);
+}
+
+template <typename T, int DPAD>
+__global__ void __launch_bounds__(kPrefillThreads, 1)
+    prefill_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ PrefillKParams p) {
+    using Cfg = PrefillCfg<DPAD>;
+    constexpr int kNQ = Cfg::kNQ;
+    constexpr int kStages = Cfg::kStages;
+    constexpr int kBM = Cfg::kBM, kBN = Cfg::kBN;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* q_smem = smem;
+    uint8_t* ring = smem + Cfg::kQBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kBarOffset);
+    uint64_t* q_full = bars;                 // [2]
+    uint64_t* s_full = bars + 2;             // [2]
+    uint64_t* p_full = bars + 4;             // [2]
+    uint64_t* o_full = bars + 6;             // [2]
+    uint64_t* tail_bar = bars + 8;           // [1]
+    uint64_t* kv_full = bars + 9;            // [kStages]
+    uint64_t* kv_empty = kv_full + kStages;  // [kStages]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(kv_empty + kStages);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    // ---- work item.  Causal: heaviest (largest m) blocks first.
+    const int mblk = p.is_causal ? (p.num_m_blocks - 1 - (int)blockIdx.x) : (int)blockIdx.x;
+    const int h = blockIdx.y;
+    const int b = blockIdx.z;
+    const int kh = h / p.group;
+    int q_off = 0, k_off = 0, len_q = p.seqlen_q, len_k = p.seqlen_k;
+    if (p.cu_seqlens_q) {
+        q_off = p.cu_seqlens_q[b];
+        len_q = p.cu_seqlens_q[b + 1] - q_off;
+        k_off = p.cu_seqlens_k[b];
+        len_k = p.cu_seqlens_k[b + 1] - k_off;
+    }
+    const int m0 = mblk * (kNQ * kBM);
+    if (m0 >= len_q) return;   // whole CTA exits before any allocation (prefill.cuh:724-726)
+
+    const int n_tiles_k = (len_k + kBN - 1) / kBN;
+    int n_i[2] = {0, 0};
+#pragma unroll
+    for (int i = 0; i < kNQ; ++i) {
+        const int r0 = m0 + i * kBM;
+        if (r0 < len_q) n_i[i] = p.is_causal ? min(n_tiles_k, r0 / kBN + 1) : n_tiles_k;
+    }
+    const int n_max = max(n_i[0], n_i[1]);
+
+    // ---- one-time setup
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&q_full[i], 1);
+            mbar_init(&s_full[i], 1);
+            mbar_init(&p_full[i], 128);
+            mbar_init(&o_full[i], 1);
+        }
+        mbar_init(tail_bar, 1);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&kv_full[s], 1);
+            mbar_init(&kv_empty[s], 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 10) {
+        tmem_alloc(tmem_slot, Cfg::kTmemCols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // Register re-balancing: the launch gives every thread 168 registers (65536 / 384 threads); the
+    // data-movement warpgroup hands most of its share to the two softmax warpgroups (whole S row in registers).
+    // (Each setmaxnreg sits at the top of its own role branch so that ptxas sees the budget per region.)
+    if (warp >= 8) {
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    if (warp == 8) {
+        // ======================================================================= TMA producer
+        if (lane == 0) {
+            prefetch_tensormap(&tmQ);
+            prefetch_tensormap(&tmK);
+            prefetch_tensormap(&tmV);
+        }
+        const int q_row_coord = p.cu_seqlens_q ? (q_off + m0) : m0;
+        const int q_b_coord = p.cu_seqlens_q ? 0 : b;
+        if (lane == 0) {
+#pragma unroll
+            for (int i = 0; i < kNQ; ++i) {
+                if (n_i[i] > 0) {
+                    mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
+#pragma unroll
+                    for (int sb = 0; sb < Cfg::kSub; ++sb)
+                        tma_load_4d(q_smem + i * Cfg::kQTileBytes + sb * Cfg::kSubBytes, &tmQ, &q_full[i], sb * 64,
+                                    q_row_coord + i * kBM, h, q_b_coord);
+                }
+            }
+        }
+        const int32_t* bt = p.block_table ? p.block_table + (int64_t)b * p.block_table_batch_stride : nullptr;
+        const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
+        // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
+        // batches TMA's out-of-bounds fill does it; for packed / paged K/V the producer warp zeroes them.
+        const bool need_tail_fix = (bt != nullptr) || packed_k;
+        uint32_t tail_phase = 0;
+        int it = 0;
+        for (int j = 0; j < n_max; ++j) {
+            const int row0 = j * kBN;
+            const int rows_valid = min(len_k - row0, kBN);
+#pragma unroll 1
+            for (int kv = 0; kv < 2; ++kv, ++it) {
+                const int s = it % kStages;
+                const uint32_t ph = (it / kStages) & 1;
+                const CUtensorMap* tm = kv ? &tmV : &tmK;
+                uint8_t* dst = ring + s * Cfg::kKVTileBytes;
+                const bool fix = kv && need_tail_fix && rows_valid < kBN;
+                uint64_t* bar = fix ? tail_bar : &kv_full[s];
+                if (lane == 0) {
+                    mbar_wait(&kv_empty[s], ph ^ 1);
+                    if (bt) {
+                        const int nchunks = (rows_valid + p.kv_box_rows - 1) / p.kv_box_rows;
+                        const int chunk_bytes = p.kv_box_rows * 128;
+                        mbar_arrive_expect_tx(bar, (uint32_t)(nchunks * chunk_bytes * Cfg::kSub));
+                        for (int c = 0; c < nchunks; ++c) {
+                            const int row = row0 + c * p.kv_box_rows;
+                            const int pg = row / p.page;
+                            const int in_page = row - pg * p.page;
+                            const int blk = bt[pg];
+#pragma unroll
+                            for (int sb = 0; sb < Cfg::kSub; ++sb)
+                                tma_load_4d(dst + sb * Cfg::kSubBytes + c * chunk_bytes, tm, bar, sb * 64, in_page, kh,
+                                            blk);
+                        }
+                    } else {
+                        mbar_arrive_expect_tx(bar, Cfg::kKVTileBytes);
+#pragma unroll
+                        for (int sb = 0; sb < Cfg::kSub; ++sb)
+                            tma_load_4d(dst + sb * Cfg::kSubBytes, tm, bar, sb * 64, (packed_k ? k_off : 0) + row0, kh,
+                                        packed_k ? 0 : b);
+                    }
+                }
+                if (fix) {
+                    // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
+                    mbar_wait(tail_bar, tail_phase);
+                    tail_phase ^= 1;
+                    for (int r = rows_valid; r < kBN; ++r) {
+#pragma unroll
+                        for (int sb = 0; sb < Cfg::kSub; ++sb)
+                            *reinterpret_cast<uint32_t*>(dst + sb * Cfg::kSubBytes + r * 128 + lane * 4) = 0u;
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&kv_full[s]);
+                }
+            }
+        }
+    } else if (warp == 9) {
+        // ======================================================================= MMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idescS = umma_idesc_f16(Elem<T>::kFmt, kBM, kBN, 0, 0);
+            constexpr uint32_t idescO = umma_idesc_f16(Elem<T>::kFmt, kBM, DPAD, 0, 1);
+            const uint32_t q_addr = smem_u32(q_smem);
+            const uint32_t ring_addr = smem_u32(ring);
+
+            auto issue_S = [&](int i, int stage) {
+                const uint32_t qa = q_addr + i * Cfg::kQTileBytes;
+                const uint32_t ka = ring_addr + stage * Cfg::kKVTileBytes;
+#pragma unroll
+                for (int ks = 0; ks < DPAD / 16; ++ks)
+                    umma_ss(tmem_base + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
+                            ks > 0 ? 1u : 0u);
+                umma_commit(&s_full[i]);
+            };
+            auto issue_PV = [&](int i, int stage, bool accumulate) {
+                const uint32_t va = ring_addr + stage * Cfg::kKVTileBytes;
+#pragma unroll
+                for (int ks = 0; ks < kBN / 16; ++ks)
+                    umma_ts(tmem_base + Cfg::kTmemO + i * DPAD, tmem_base + Cfg::kTmemS + i * 128 + ks * 8,
+                            desc_mnmajor(va, ks), idescO, (accumulate || ks > 0) ? 1u : 0u);
+                umma_commit(&o_full[i]);
+            };
+
+#pragma unroll
+            for (int i = 0; i < kNQ; ++i)
+                if (n_i[i] > 0) mbar_wait(&q_full[i], 0);
+            int it = 0;
+            if (n_max > 0) {
+                const int sK = it % kStages;
+                mbar_wait(&kv_full[sK], (it / kStages) & 1);
+                ++it;
+                tc_fence_after();
+#pragma unroll
+                for (int i = 0; i < kNQ; ++i)
+                    if (n_i[i] > 0) issue_S(i, sK);
+                umma_commit(&kv_empty[sK]);
+            }
+            for (int j = 0; j < n_max; ++j) {
+                const int sV = it % kStages;
+                mbar_wait(&kv_full[sV], (it / kStages) & 1);
+                ++it;
+                const bool has_next = (j + 1 < n_max);
+                int sK = 0;
+                if (has_next) {
+                    sK = it % kStages;
+                    mbar_wait(&kv_full[sK], (it / kStages) & 1);
+                    ++it;
+                }
+                tc_fence_after();
+#pragma unroll
+                for (int i = 0; i < kNQ; ++i) {
+                    if (j < n_i[i]) {
+                        mbar_wait(&p_full[i], j & 1);
+                        tc_fence_after();
+                        issue_PV(i, sV, j > 0);
+                    }
+                    if (j + 1 < n_i[i]) issue_S(i, sK);
+                }
+                umma_commit(&kv_empty[sV]);
+                if (has_next) umma_commit(&kv_empty[sK]);
+            }
+        }
+    }
+    } else {
+      asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+      if (warp < 4 * kNQ) {
+        // ======================================================================= softmax warpgroups
+        const int i = warp >> 2;
+        const int row_in_tile = (warp & 3) * 32 + lane;
+        const int qrow = m0 + i * kBM + row_in_tile;            // row inside the sequence
+        const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+        const uint32_t tS = tmem_base + lane_sel + Cfg::kTmemS + i * 128;
+        const uint32_t tO = tmem_base + lane_sel + Cfg::kTmemO + i * DPAD;
+        const int n_mine = n_i[i];
+        const float c2 = p.scale_log2;
+        float m_run = -INFINITY, l_run = 0.f;
+
+        for (int j = 0; j < n_mine; ++j) {
+            mbar_wait(&s_full[i], j & 1);
+            tc_fence_after();
+            uint32_t su[128];   // this thread's S row (fp32 bit patterns)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&su[c * 32]));
+            tmem_wait_ld();
+
+            const int col0 = j * kBN;
+            const bool need_mask = (col0 + kBN > len_k) || (p.is_causal && (col0 + kBN - 1 > m0 + i * kBM));
+            if (need_mask) {
+                const int lim = p.is_causal ? min(len_k, qrow + 1) : len_k;   // cols >= lim are masked
+#pragma unroll
+                for (int c = 0; c < 128; ++c)
+                    if (col0 + c >= lim) su[c] = 0xff800000u;   // -inf
+            }
+            float tmax = __uint_as_float(su[0]);
+#pragma unroll
+            for (int c = 1; c < 128; ++c) tmax = fmaxf(tmax, __uint_as_float(su[c]));
+            const float m_new = fmaxf(m_run, tmax);
+            // lazy rescale: keep the stale max unless it grew by more than 2^8
+            const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
+            const float m_use = grow ? m_new : m_run;
+            const float factor = grow ? ((m_run == -INFINITY) ? 0.f : exp2f((m_run - m_new) * c2)) : 1.f;
+            const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
+            m_run = m_use;
+
+            float psum = 0.f;
+            uint32_t pk[64];
+#pragma unroll
+            for (int c = 0; c < 64; ++c) {
+                const float p0 = ex2_approx(fmaf(__uint_as_float(su[2 * c]), c2, -ms));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(su[2 * c + 1]), c2, -ms));
+                psum += p0 + p1;
+                pk[c] = Elem<T>::pack(p0, p1);
+            }
+            l_run = l_run * factor + psum;
+
+            if (j > 0 && __any_sync(0xffffffffu, grow)) {
+                // O_i currently holds sum_{t<j} P_t V_t: wait for PV(j-1), then rescale our row in place
+                mbar_wait(&o_full[i], (j - 1) & 1);
+                tc_fence_after();
+#pragma unroll
+                for (int c = 0; c < DPAD / 32; ++c) {
+                    uint32_t o[32];
+                    tmem_ld32(tO + c * 32, o);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * factor);
+                    tmem_st32(tO + c * 32, o);
+                }
+            }
+            tmem_st32(tS, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+            tmem_st32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(&p_full[i]);
+        }
+
+        // ---- epilogue: O / l -> out dtype -> global (row-guarded)
+        if (qrow < len_q) {
+            T* orow = static_cast<T*>(p.o) + (int64_t)h * p.o_head_stride +
+                      (p.cu_seqlens_q ? (int64_t)(q_off + qrow) * p.o_row_stride
+                                      : (int64_t)b * p.o_batch_stride + (int64_t)qrow * p.o_row_stride);
+            if (n_mine > 0) {
+                mbar_wait(&o_full[i], (n_mine - 1) & 1);
+                tc_fence_after();
+            }
+            const float inv = (l_run == 0.f || l_run != l_run) ? 1.f : 1.f / l_run;   // prefill.cuh:604-605
+#pragma unroll
+            for (int c = 0; c < DPAD / 32; ++c) {
+                uint32_t o[32];
+                if (n_mine > 0) {
+                    tmem_ld32(tO + c * 32, o);
+                    tmem_wait_ld();
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) o[e] = 0u;
+                }
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    if (c * 32 + v * 8 < p.head_dim) {
+                        uint4 w;
+                        w.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
+                        w.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
+                        w.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
+                        w.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
+                        *reinterpret_cast<uint4*>(orow + c * 32 + v * 8) = w;
+                    }
+                }
+            }
+        } else if (n_mine > 0) {
+            // rows past the sequence end still have to let the last PV drain before TMEM is freed
+            mbar_wait(&o_full[i], (n_mine - 1) & 1);
+        }
+      }
+    }
+
+    // ---- teardown
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 10) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    }
+}
+
+}  // namespace
+
+template <typename T, int DPAD>
+static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                                    const PrefillKParams& p, cudaStream_t stream) {
+    using Cfg = PrefillCfg<DPAD>;
+    auto kern = prefill_fwd_kernel<T, DPAD>;
+    static bool attr_done[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && !attr_done[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        if (e != cudaSuccess) return e;
+        attr_done[dev] = true;
+    }
+    dim3 grid(p.num_m_blocks, p.heads, p.batch);
+    kern<<<grid, kPrefillThreads, Cfg::kSmemBytes, stream>>>(tmQ, tmK, tmV, p);
+    return cudaGetLastError();
+}
+
+int prefill_rows_per_cta(int dpad) { return (dpad <= 128 ? 2 : 1) * kPrefillBlockM; }
+
+cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                           const PrefillKParams& p, bool is_bf16, int dpad, cudaStream_t stream) {
+#define MFA_PREFILL_CASE(DP)                                                                     \
+    case DP:                                                                                     \
+        return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP>(tmQ, tmK, tmV, p, stream)           \
+                       : launch_prefill_t<__half, DP>(tmQ, tmK, tmV, p, stream);
+    switch (dpad) {
+        MFA_PREFILL_CASE(64)
+        MFA_PREFILL_CASE(128)
+        MFA_PREFILL_CASE(256)
+        default:
+            return cudaErrorInvalidValue;
+    }
+#undef MFA_PREFILL_CASE
+}
+
+}  // namespace mfa

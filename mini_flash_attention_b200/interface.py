@@ -1,0 +1,91 @@
+"""Public Python API -- signatures verbatim from the reference
+(/root/reference/mini_flash_attention/interface.py:6-11, :40-50, :95-102).
+
+Each function is, like in the reference, a one-line positional forward into the extension surface
+(here ``mini_flash_attention_b200._C``, a C-ABI shim instead of a pybind module).
+"""
+from __future__ import annotations
+
+from typing import Optional, Union
+
+import torch
+
+from . import _C
+
+
+def flash_attn_func(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    causal: bool = False,
+) -> torch.Tensor:
+    """FlashAttention forward (reference: interface.py:6-37).
+
+    Supports MQA/GQA: K, V may have fewer heads than Q (the number of Q heads must be divisible by the number
+    of KV heads); Q head h attends to KV head ``h // (Hq // Hkv)``.
+
+    Arguments:
+        q: (batch_size, seqlen_q, nheads, headdim), fp16 or bf16, CUDA
+        k: (batch_size, seqlen_k, nheads_k, headdim)
+        v: (batch_size, seqlen_k, nheads_k, headdim)
+        causal: apply the causal mask.  Like the reference it is aligned to the TOP-LEFT corner
+            (key j is visible to query i iff j <= i), which equals the usual convention when seqlen_q == seqlen_k.
+    Return:
+        out: (batch_size, seqlen_q, nheads, headdim)
+    """
+    return _C.mini_flash_attention_forward(q, k, v, None, causal, -1, -1)
+
+
+def flash_attn_varlen_func(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    cu_seqlens_q: torch.Tensor,
+    cu_seqlens_k: torch.Tensor,
+    max_seqlen_q: int,
+    max_seqlen_k: int,
+    causal: bool = False,
+    block_table=None,
+) -> torch.Tensor:
+    """FlashAttention forward for packed variable-length batches (reference: interface.py:40-92).
+
+    Arguments:
+        q: (total_q, nheads, headdim)
+        k, v: (total_k, nheads_k, headdim), or with ``block_table`` the paged cache
+            (num_blocks, page_block_size, nheads_k, headdim)
+        cu_seqlens_q, cu_seqlens_k: (batch_size + 1,) int32 cumulative sequence lengths
+        max_seqlen_q, max_seqlen_k: maximum sequence lengths in the batch
+        causal: top-left aligned causal mask (see flash_attn_func)
+        block_table: optional (batch_size, max_blocks_per_seq) int32 page table; pages are gathered per page
+            (any page size that is a multiple of 8), not per 64-row tile.
+    Return:
+        out: (total_q, nheads, headdim)
+    """
+    return _C.mini_flash_attention_varlen_forward(
+        q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, -1, -1, block_table
+    )
+
+
+def flash_attn_with_kvcache(
+    q,
+    k_cache,
+    v_cache,
+    cache_seqlens: Optional[Union[int, torch.Tensor]] = None,
+    block_table: Optional[torch.Tensor] = None,
+    num_splits=0,
+    *,
+    causal: bool = False,
+) -> torch.Tensor:
+    """Single-token decode against a KV cache (reference: interface.py:95-124).
+
+    Arguments:
+        q: (batch_size, 1, nheads, headdim)
+        k_cache, v_cache: (batch_size, seqlen_cache, nheads_k, headdim), or with ``block_table`` the paged cache
+            (num_blocks, page_block_size, nheads_k, headdim)
+        cache_seqlens: (batch_size,) int32 current lengths; an int is broadcast; None means the full cache
+        block_table: optional (batch_size, max_blocks_per_seq) int32
+        num_splits: KV splits (flash decoding); <= 0 picks automatically
+        causal: accepted for compatibility with the reference's tests and ignored (q_len == 1)
+    """
+    assert q.size(1) == 1, "flash_attn_with_kvcache currently only supports seqlen_q=1 for decoding"
+    return _C.mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)
