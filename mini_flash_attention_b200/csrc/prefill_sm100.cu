@@ -386,8 +386,10 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             mbar_arrive(&p_full[i]);
         }
 
-        // ---- epilogue: O / l -> out dtype -> global (row-guarded)
-        if (qrow < len_q) {
+        // ---- epilogue: O / l -> out dtype -> global.  tcgen05.ld is warp-collective (.sync.aligned), so every
+        // lane takes part in the TMEM loads; only the global stores are guarded by row < len_q.
+        {
+            const bool row_ok = qrow < len_q;
             T* orow = static_cast<T*>(p.o) + (int64_t)h * p.o_head_stride +
                       (p.cu_seqlens_q ? (int64_t)(q_off + qrow) * p.o_row_stride
                                       : (int64_t)b * p.o_batch_stride + (int64_t)qrow * p.o_row_stride);
@@ -399,28 +401,27 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
 #pragma unroll
             for (int c = 0; c < DPAD / 32; ++c) {
                 uint32_t o[32];
-                if (n_mine > 0) {
+                if (n_mine > 0) {   // warp-uniform
                     tmem_ld32(tO + c * 32, o);
                     tmem_wait_ld();
                 } else {
 #pragma unroll
                     for (int e = 0; e < 32; ++e) o[e] = 0u;
                 }
+                if (row_ok) {
 #pragma unroll
-                for (int v = 0; v < 4; ++v) {
-                    if (c * 32 + v * 8 < p.head_dim) {
-                        uint4 w;
-                        w.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
-                        w.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
-                        w.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
-                        w.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
-                        *reinterpret_cast<uint4*>(orow + c * 32 + v * 8) = w;
+                    for (int v = 0; v < 4; ++v) {
+                        if (c * 32 + v * 8 < p.head_dim) {
+                            uint4 w;
+                            w.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
+                            w.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
+                            w.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
+                            w.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
+                            *reinterpret_cast<uint4*>(orow + c * 32 + v * 8) = w;
+                        }
                     }
                 }
             }
-        } else if (n_mine > 0) {
-            // rows past the sequence end still have to let the last PV drain before TMEM is freed
-            mbar_wait(&o_full[i], (n_mine - 1) & 1);
         }
       }
     }
