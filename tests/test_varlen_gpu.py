@@ -85,6 +85,8 @@ def _paged_inputs(seqlens_q, seqlens_k, H, Hkv, D, page, dtype, seed, tables=Non
     pages_per = [(l + page - 1) // page for l in seqlens_k]
     max_pages = max(pages_per)
     num_blocks = sum(pages_per) + 5
+    if tables is not None:
+        num_blocks = max(num_blocks, max(max(t) for t in tables) + 1)
     q = torch.randn(sum(seqlens_q), H, D, device="cuda", dtype=dtype, generator=g)
     kc = torch.randn(num_blocks, page, Hkv, D, device="cuda", dtype=dtype, generator=g)
     vc = torch.randn(num_blocks, page, Hkv, D, device="cuda", dtype=dtype, generator=g)
