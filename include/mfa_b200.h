@@ -125,6 +125,10 @@ int mfa_combine_partials(const float* packed, int num_partials, int rows, int he
                          void* out, int64_t out_row_stride, int is_bf16, float* lse_out,
                          void* cuda_stream);
 
+/* tuning aid: libraries built with -DMFA_TRACE write clock64() stamps of prefill CTA (0,0,0) into this device
+ * buffer ([3 roles][64 iterations][8 events] int64); a no-op in normal builds.  NULL disables. */
+void mfa_debug_set_trace(void* device_buffer);
+
 /* number of kernel launches issued by this library since load (bench.py reports it) */
 uint64_t mfa_launch_count(void);
 

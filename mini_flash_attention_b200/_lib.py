@@ -9,7 +9,8 @@ import ctypes
 import os
 
 _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG_DIR, "libmfa_b200.so")
+# MFA_B200_LIB: kernel-tuning hook (scripts/tune_prefill.py) to load an alternative build of the same ABI
+LIB_PATH = os.environ.get("MFA_B200_LIB") or os.path.join(_PKG_DIR, "libmfa_b200.so")
 
 MFA_OK = 0
 ABI_VERSION = 1
@@ -46,6 +47,7 @@ class MfaParams(ctypes.Structure):
 EXPORTS = (
     "mfa_abi_version", "mfa_last_error", "mfa_device_supported", "mfa_prefill_fwd", "mfa_decode_num_splits",
     "mfa_decode_workspace_bytes", "mfa_decode_fwd", "mfa_combine_partials", "mfa_launch_count", "mfa_selftest_umma",
+    "mfa_debug_set_trace",
 )
 
 _lib = None
@@ -80,6 +82,8 @@ def load() -> ctypes.CDLL:
                                          ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
     lib.mfa_combine_partials.restype = ctypes.c_int
     lib.mfa_launch_count.restype = ctypes.c_uint64
+    lib.mfa_debug_set_trace.argtypes = [ctypes.c_void_p]
+    lib.mfa_debug_set_trace.restype = None
     lib.mfa_selftest_umma.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                       ctypes.c_int, ctypes.c_int, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]
     lib.mfa_selftest_umma.restype = ctypes.c_int

@@ -42,6 +42,31 @@ def _stale(target: str, deps) -> bool:
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
+def build_variant(name: str, defines, verbose: bool = False) -> str:
+    """Tuning aid: build csrc/ with extra -D flags into mini_flash_attention_b200/variants/lib<name>.so."""
+    vdir = os.path.join(PKG_DIR, "variants")
+    odir = os.path.join(vdir, "_obj_" + name)
+    os.makedirs(odir, exist_ok=True)
+    out = os.path.join(vdir, f"lib{name}.so")
+    nvcc = _nvcc()
+
+    def one(src):
+        obj = os.path.join(odir, os.path.basename(src) + ".o")
+        cmd = [nvcc] + NVCC_FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-I", CSRC, "-c", src, "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode:
+            raise RuntimeError(r.stdout + r.stderr)
+        if verbose:
+            print(r.stderr)
+        return obj
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        objs = list(ex.map(one, [os.path.join(CSRC, s) for s in SOURCES]))
+    r = subprocess.run([nvcc, "-shared", "-o", out] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"], capture_output=True, text=True)
+    if r.returncode:
+        raise RuntimeError(r.stdout + r.stderr)
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     hdrs = [h if os.path.isabs(h) else os.path.join(CSRC, h) for h in HEADERS]

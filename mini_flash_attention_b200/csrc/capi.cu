@@ -28,6 +28,7 @@ int prefill_rows_per_cta(int dpad);
 namespace {
 
 thread_local char g_err[512] = "";
+long long* g_trace = nullptr;   // tuning aid, see mfa_debug_set_trace
 std::atomic<uint64_t> g_launches{0};
 
 int fail(int code, const char* fmt, ...) {
@@ -100,6 +101,7 @@ bool mult8(int64_t x) { return (x % 8) == 0; }
 extern "C" {
 
 int mfa_abi_version(void) { return MFA_B200_ABI_VERSION; }
+void mfa_debug_set_trace(void* device_buffer) { g_trace = static_cast<long long*>(device_buffer); }
 const char* mfa_last_error(void) { return g_err; }
 uint64_t mfa_launch_count(void) { return g_launches.load(); }
 
@@ -192,6 +194,7 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);   // api.cpp:99
     kp.scale_log2 = kp.scale * 1.4426950408889634f;                                      // api.cpp:100
     kp.lse = nullptr;
+    kp.trace = g_trace;
 
     cudaError_t e = mfa::launch_prefill(tmQ, tmK, tmV, kp, bf16, dpad, static_cast<cudaStream_t>(cuda_stream));
     if (e != cudaSuccess) return cuda_fail(e, "prefill launch");

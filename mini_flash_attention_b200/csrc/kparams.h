@@ -64,6 +64,7 @@ struct PrefillKParams {
     int32_t num_m_blocks;          // ceil(seqlen_q / 256)
     float scale, scale_log2;
     float* lse;                    // optional (B, H, Sq) / (H, total_q): not exposed yet
+    long long* trace;              // MFA_TRACE builds only: clock64() stamps of CTA (0,0,0), [role][iter][8]
 };
 
 }  // namespace mfa

@@ -34,6 +34,19 @@
 #include "kparams.h"
 #include "ptx.cuh"
 
+#ifndef MFA_POLY_MASK
+#define MFA_POLY_MASK 0xAu   // pairs 1 and 3 of every 4 -> half of the exponentials off the MUFU
+#endif
+
+#ifdef MFA_TRACE
+#define MFA_TR(role, it, ev)                                                                              \
+    do {                                                                                                  \
+        if (tr_on && (it) < 64) p.trace[((role) * 64 + (it)) * 8 + (ev)] = clock64();                      \
+    } while (0)
+#else
+#define MFA_TR(role, it, ev) do { } while (0)
+#endif
+
 namespace mfa {
 
 namespace {
@@ -75,6 +88,7 @@ struct PrefillCfg {
     static constexpr uint32_t kTmemS = 0;                        // S_i at kTmemS + i*128
     static constexpr uint32_t kTmemO = 256;                      // O_i at kTmemO + i*DPAD
     static constexpr float kRescaleThreshold = 8.0f;             // log2 domain
+    static constexpr uint32_t kPolyMask = MFA_POLY_MASK;         // column pairs (c & 3) whose exp2 runs on the FMA pipe
 };
 
 // smem descriptors -------------------------------------------------------------------------------
@@ -88,6 +102,32 @@ __device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_addr, int kstep) {
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep) {
     const uint32_t addr = tile_addr + kstep * (16 * 128);
     return umma_smem_desc(addr, /*LBO*/ 128 * 128, /*SBO*/ 1024, /*SW128*/ 2);
+}
+
+// 2^x for two packed floats, x <= ~8, on the FMA pipe: clamp, round-to-nearest split x = n + f (|f| <= 0.5) with
+// the 1.5*2^23 magic constant, 2^f by a degree-3 polynomial with p(0) == 1 exactly (max rel. error 1.0e-4, below
+// the half-ulp of the fp16/bf16 P it is rounded to), exponent added with one integer shift-add.
+// x <= -127 gives exactly +0 (masked columns hold -inf).
+__device__ __forceinline__ uint64_t exp2_poly2(uint64_t x2) {
+    float x0, x1;
+    f2_unpack(x2, x0, x1);
+    x0 = fmaxf(x0, -127.f);
+    x1 = fmaxf(x1, -127.f);
+    const uint64_t xc = f2_pack(x0, x1);
+    const uint64_t magic = f2_pack(12582912.f, 12582912.f);
+    const uint64_t nmagic = f2_pack(-12582912.f, -12582912.f);
+    const uint64_t t = f2_add(xc, magic);
+    const uint64_t n = f2_add(t, nmagic);
+    const uint64_t f = f2_fma(n, f2_pack(-1.f, -1.f), xc);
+    uint64_t q = f2_fma(f, f2_pack(0.05500871315598488f, 0.05500871315598488f), f2_pack(0.24221068620681763f, 0.24221068620681763f));
+    q = f2_fma(q, f, f2_pack(0.6932829022407532f, 0.6932829022407532f));
+    q = f2_fma(q, f, f2_pack(1.f, 1.f));
+    float t0, t1, q0, q1;
+    f2_unpack(t, t0, t1);
+    f2_unpack(q, q0, q1);
+    const float r0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+    const float r1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
+    return f2_pack(r0, r1);
 }
 
 template <typename T, int DPAD>
@@ -106,15 +146,19 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kBarOffset);
     uint64_t* q_full = bars;                 // [2]
     uint64_t* s_full = bars + 2;             // [2]
-    uint64_t* p_full = bars + 4;             // [2]
+    uint64_t* p_lo = bars + 4;               // [2]  first half of P_i (KV rows 0-63) written
     uint64_t* o_full = bars + 6;             // [2]
     uint64_t* tail_bar = bars + 8;           // [1]
-    uint64_t* kv_full = bars + 9;            // [kStages]
+    uint64_t* p_hi = bars + 9;               // [2]  second half of P_i
+    uint64_t* kv_full = bars + 11;           // [kStages]
     uint64_t* kv_empty = kv_full + kStages;  // [kStages]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(kv_empty + kStages);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+#ifdef MFA_TRACE
+    const bool tr_on = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp == 9 || (warp & 3) == 0);
+#endif
 
     // ---- work item.  Causal: heaviest (largest m) blocks first.
     const int mblk = p.is_causal ? (p.num_m_blocks - 1 - (int)blockIdx.x) : (int)blockIdx.x;
@@ -145,7 +189,8 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
         for (int i = 0; i < 2; ++i) {
             mbar_init(&q_full[i], 1);
             mbar_init(&s_full[i], 1);
-            mbar_init(&p_full[i], 128);
+            mbar_init(&p_lo[i], 128);
+            mbar_init(&p_hi[i], 128);
             mbar_init(&o_full[i], 1);
         }
         mbar_init(tail_bar, 1);
@@ -249,28 +294,42 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
         }
     } else if (warp == 9) {
         // ======================================================================= MMA issuer
-        if (lane == 0) {
+        // The whole warp runs the (warp-uniform) control flow and the barrier waits; one elected lane issues the
+        // tcgen05 instructions.  Written this way -- not `if (lane == 0)` -- so that ptxas keeps descriptors and
+        // addresses in uniform registers instead of wrapping every UTCHMMA in an ELECT/R2UR waterfall loop
+        // (measured: ~110 cycles per issued MMA with the loop, which made the issue thread the bottleneck).
+        {
             constexpr uint32_t idescS = umma_idesc_f16(Elem<T>::kFmt, kBM, kBN, 0, 0);
             constexpr uint32_t idescO = umma_idesc_f16(Elem<T>::kFmt, kBM, DPAD, 0, 1);
             const uint32_t q_addr = smem_u32(q_smem);
             const uint32_t ring_addr = smem_u32(ring);
 
             auto issue_S = [&](int i, int stage) {
-                const uint32_t qa = q_addr + i * Cfg::kQTileBytes;
-                const uint32_t ka = ring_addr + stage * Cfg::kKVTileBytes;
+                if (elect_one()) {
+                    const uint32_t qa = q_addr + i * Cfg::kQTileBytes;
+                    const uint32_t ka = ring_addr + stage * Cfg::kKVTileBytes;
 #pragma unroll
-                for (int ks = 0; ks < DPAD / 16; ++ks)
-                    umma_ss(tmem_base + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
-                            ks > 0 ? 1u : 0u);
-                umma_commit(&s_full[i]);
+                    for (int ks = 0; ks < DPAD / 16; ++ks)
+                        umma_ss(tmem_base + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
+                                ks > 0 ? 1u : 0u);
+                    umma_commit(&s_full[i]);
+                }
+                __syncwarp();
             };
-            auto issue_PV = [&](int i, int stage, bool accumulate) {
-                const uint32_t va = ring_addr + stage * Cfg::kKVTileBytes;
+            auto issue_PV = [&](int i, int stage, bool accumulate, int ks0, int ks1, bool commit_o) {
+                if (elect_one()) {
+                    const uint32_t va = ring_addr + stage * Cfg::kKVTileBytes;
 #pragma unroll
-                for (int ks = 0; ks < kBN / 16; ++ks)
-                    umma_ts(tmem_base + Cfg::kTmemO + i * DPAD, tmem_base + Cfg::kTmemS + i * 128 + ks * 8,
-                            desc_mnmajor(va, ks), idescO, (accumulate || ks > 0) ? 1u : 0u);
-                umma_commit(&o_full[i]);
+                    for (int ks = ks0; ks < ks1; ++ks)
+                        umma_ts(tmem_base + Cfg::kTmemO + i * DPAD, tmem_base + Cfg::kTmemS + i * 128 + ks * 8,
+                                desc_mnmajor(va, ks), idescO, (accumulate || ks > 0) ? 1u : 0u);
+                    if (commit_o) umma_commit(&o_full[i]);
+                }
+                __syncwarp();
+            };
+            auto commit = [&](uint64_t* bar) {
+                if (elect_one()) umma_commit(bar);
+                __syncwarp();
             };
 
 #pragma unroll
@@ -285,7 +344,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i)
                     if (n_i[i] > 0) issue_S(i, sK);
-                umma_commit(&kv_empty[sK]);
+                commit(&kv_empty[sK]);
             }
             for (int j = 0; j < n_max; ++j) {
                 const int sV = it % kStages;
@@ -299,17 +358,24 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     ++it;
                 }
                 tc_fence_after();
+                MFA_TR(2, j, 0);
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i) {
                     if (j < n_i[i]) {
-                        mbar_wait(&p_full[i], j & 1);
+                        mbar_wait(&p_lo[i], j & 1);
                         tc_fence_after();
-                        issue_PV(i, sV, j > 0);
+                        MFA_TR(2, j, 1 + 3 * i);
+                        issue_PV(i, sV, j > 0, 0, kBN / 32, false);
+                        mbar_wait(&p_hi[i], j & 1);
+                        tc_fence_after();
+                        MFA_TR(2, j, 2 + 3 * i);
+                        issue_PV(i, sV, j > 0, kBN / 32, kBN / 16, true);
                     }
                     if (j + 1 < n_i[i]) issue_S(i, sK);
+                    MFA_TR(2, j, 3 + 3 * i);
                 }
-                umma_commit(&kv_empty[sV]);
-                if (has_next) umma_commit(&kv_empty[sK]);
+                commit(&kv_empty[sV]);
+                if (has_next) commit(&kv_empty[sK]);
             }
         }
     }
@@ -328,12 +394,15 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
         float m_run = -INFINITY, l_run = 0.f;
 
         for (int j = 0; j < n_mine; ++j) {
+            MFA_TR(i, j, 0);
             mbar_wait(&s_full[i], j & 1);
             tc_fence_after();
+            MFA_TR(i, j, 1);
             uint32_t su[128];   // this thread's S row (fp32 bit patterns)
 #pragma unroll
             for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&su[c * 32]));
             tmem_wait_ld();
+            MFA_TR(i, j, 2);
 
             const int col0 = j * kBN;
             const bool need_mask = (col0 + kBN > len_k) || (p.is_causal && (col0 + kBN - 1 > m0 + i * kBM));
@@ -343,9 +412,17 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 for (int c = 0; c < 128; ++c)
                     if (col0 + c >= lim) su[c] = 0xff800000u;   // -inf
             }
-            float tmax = __uint_as_float(su[0]);
+            // row max: 8 independent 3-input max chains, then a tree
+            float mx[8];
 #pragma unroll
-            for (int c = 1; c < 128; ++c) tmax = fmaxf(tmax, __uint_as_float(su[c]));
+            for (int a = 0; a < 8; ++a) mx[a] = fmaxf(__uint_as_float(su[a * 16]), __uint_as_float(su[a * 16 + 1]));
+#pragma unroll
+            for (int a = 0; a < 8; ++a) {
+#pragma unroll
+                for (int c = 2; c < 16; c += 2)
+                    mx[a] = fmax3(mx[a], __uint_as_float(su[a * 16 + c]), __uint_as_float(su[a * 16 + c + 1]));
+            }
+            const float tmax = fmaxf(fmax3(mx[0], mx[1], mx[2]), fmax3(fmax3(mx[3], mx[4], mx[5]), mx[6], mx[7]));
             const float m_new = fmaxf(m_run, tmax);
             // lazy rescale: keep the stale max unless it grew by more than 2^8
             const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
@@ -354,19 +431,9 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
             m_run = m_use;
 
-            float psum = 0.f;
-            uint32_t pk[64];
-#pragma unroll
-            for (int c = 0; c < 64; ++c) {
-                const float p0 = ex2_approx(fmaf(__uint_as_float(su[2 * c]), c2, -ms));
-                const float p1 = ex2_approx(fmaf(__uint_as_float(su[2 * c + 1]), c2, -ms));
-                psum += p0 + p1;
-                pk[c] = Elem<T>::pack(p0, p1);
-            }
-            l_run = l_run * factor + psum;
-
             if (j > 0 && __any_sync(0xffffffffu, grow)) {
-                // O_i currently holds sum_{t<j} P_t V_t: wait for PV(j-1), then rescale our row in place
+                // O_i currently holds sum_{t<j} P_t V_t: wait for PV(j-1), then rescale our row in place.
+                // Must happen before any part of P(j) is released to the MMA warp.
                 mbar_wait(&o_full[i], (j - 1) & 1);
                 tc_fence_after();
 #pragma unroll
@@ -379,11 +446,45 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     tmem_st32(tO + c * 32, o);
                 }
             }
-            tmem_st32(tS, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
-            tmem_st32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
-            tmem_wait_st();
-            tc_fence_before();
-            mbar_arrive(&p_full[i]);
+
+            // P = exp2(S*c2 - ms): packed FFMA2 for the scale; per pair of columns either two MUFU.EX2 or the
+            // degree-3 Cody-Waite polynomial on the FMA pipe (pairs with (c & 3) in kPolyMask), because at 128x128
+            // tiles the 16 MUFU lanes/clk cost as many cycles as the two MMAs.  Released to the MMA warp in two
+            // halves so that P.V k-steps 0-3 run while the second half is still being exponentiated.
+            MFA_TR(i, j, 3);
+            const uint64_t c2_2 = f2_pack(c2, c2);
+            const uint64_t nms_2 = f2_pack(-ms, -ms);
+            uint64_t sum2[2] = {0ull, 0ull};
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+                uint32_t pk[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    const int e = hf * 64 + 2 * c;
+                    uint64_t x2 = f2_fma(f2_pack(__uint_as_float(su[e]), __uint_as_float(su[e + 1])), c2_2, nms_2);
+                    uint64_t p2;
+                    if ((Cfg::kPolyMask >> (c & 3)) & 1) {
+                        p2 = exp2_poly2(x2);
+                    } else {
+                        float x0, x1;
+                        f2_unpack(x2, x0, x1);
+                        p2 = f2_pack(ex2_fast(x0), ex2_fast(x1));
+                    }
+                    sum2[c & 1] = f2_add(sum2[c & 1], p2);
+                    float p0, p1;
+                    f2_unpack(p2, p0, p1);
+                    pk[c] = Elem<T>::pack(p0, p1);
+                }
+                tmem_st32(tS + hf * 32, pk);
+                tmem_wait_st();
+                tc_fence_before();
+                mbar_arrive(hf == 0 ? &p_lo[i] : &p_hi[i]);
+                MFA_TR(i, j, 4 + hf);
+            }
+            float sa, sb, sc, sd;
+            f2_unpack(sum2[0], sa, sb);
+            f2_unpack(sum2[1], sc, sd);
+            l_run = l_run * factor + ((sa + sb) + (sc + sd));
         }
 
         // ---- epilogue: O / l -> out dtype -> global.  tcgen05.ld is warp-collective (.sync.aligned), so every
