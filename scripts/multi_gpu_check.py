@@ -1,0 +1,147 @@
+#!/usr/bin/env python
+"""Multi-GPU leg of the hot path on real GPUs, one process per GPU over NCCL:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
+        scripts/multi_gpu_check.py [--quick]
+
+1. parity: KV-sharded decode (partial O + LSE per rank -> ONE all_gather -> combine kernel) against the fp32
+   oracle on the full, unsharded problem (paged cache, ragged lengths, GQA);
+2. parity: prefill sharded by (batch, kv-head) with no collective, every rank's shard against the oracle;
+3. timing (device events, max over ranks): long-context decode KV = 128K ... 1M rows split over the ranks,
+   B=1, Hq=32, Hkv=8, D=128, and head-sharded prefill S=16K.
+Rank 0 prints one JSON line per measurement (also appended to gpurun_out/multigpu.jsonl when that directory exists).
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def emit(rank, rec):
+    if rank != 0:
+        return
+    line = json.dumps(rec)
+    print(line, flush=True)
+    d = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(d):
+        with open(os.path.join(d, "multigpu.jsonl"), "a") as f:
+            f.write(line + "\n")
+
+
+def timed(fn, steps, warmup, world):
+    for _ in range(warmup):
+        fn()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--quick", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import mini_flash_attention as mfa  # noqa: F401
+    from mini_flash_attention_b200 import parallel as P
+    from oracle import ref_attention as R
+
+    dt = torch.bfloat16
+    tol = 1e-2
+    # ------------------------------------------------------------------ 1. KV-sharded decode parity
+    g = torch.Generator(device="cuda").manual_seed(1234)      # same seed on every rank: same full problem
+    B, Hq, Hkv, D, page = 3, 16, 4, 128, 64
+    cap = 2048                                                 # rows of capacity per sequence
+    nblk = B * cap // page
+    q = torch.randn(B, 1, Hq, D, device="cuda", dtype=dt, generator=g)
+    kc = torch.randn(nblk, page, Hkv, D, device="cuda", dtype=dt, generator=g)
+    vc = torch.randn(nblk, page, Hkv, D, device="cuda", dtype=dt, generator=g)
+    bt = torch.randperm(nblk, device="cuda", generator=g).reshape(B, cap // page).int()
+    lens = torch.tensor([2048, 700, 1], dtype=torch.int32, device="cuda")
+    rows = P.kv_shard_rows(cap, world, align=page)
+    out = P.decode_kv_sharded(q, kc, vc, P.kv_shard_lengths(lens, rank, rows), P.kv_shard_block_table(bt, rank, rows, page),
+                              world=world)
+    ref = R.kvcache_ref(q, kc, vc, lens, bt)
+    err = (out.float() - ref).abs().max()
+    if world > 1:
+        dist.all_reduce(err, op=dist.ReduceOp.MAX)
+    emit(rank, {"check": "decode_kv_sharded parity", "world": world, "max_abs_err": float(err), "tol": tol,
+                "ok": bool(float(err) <= tol)})
+    assert float(err) <= tol, float(err)
+
+    # ------------------------------------------------------------------ 2. sharded prefill parity
+    Bp, Sp, Hp, Hkp = 2, 384, 8, 2
+    qp = torch.randn(Bp, Sp, Hp, D, device="cuda", dtype=dt, generator=g)
+    kp = torch.randn(Bp, Sp, Hkp, D, device="cuda", dtype=dt, generator=g)
+    vp = torch.randn(Bp, Sp, Hkp, D, device="cuda", dtype=dt, generator=g)
+    o_sh, shard = P.prefill_sharded(qp, kp, vp, True, rank=rank, world=world)
+    full_ref = R.attention_ref(qp, kp, vp, True)
+    perr = torch.zeros((), device="cuda")
+    if o_sh is not None:
+        grp = Hp // Hkp
+        h_lo, h_hi = shard.q_heads(grp)
+        perr = (o_sh.float() - full_ref[shard.batch_lo:shard.batch_hi, :, h_lo:h_hi]).abs().max()
+    if world > 1:
+        dist.all_reduce(perr, op=dist.ReduceOp.MAX)
+    emit(rank, {"check": "prefill_sharded parity", "world": world, "max_abs_err": float(perr), "tol": tol,
+                "ok": bool(float(perr) <= tol)})
+    assert float(perr) <= tol, float(perr)
+
+    # ------------------------------------------------------------------ 3. timings
+    Bl, Hq, Hkv, page = 1, 32, 8, 256
+    kv_list = [131072] if args.quick else [131072, 262144, 524288, 1048576]
+    for KV in kv_list:
+        rows = P.kv_shard_rows(KV, world, align=page)
+        nb = Bl * rows // page
+        ql = torch.randn(Bl, 1, Hq, D, device="cuda", dtype=dt, generator=g)
+        kl = torch.randn(nb, page, Hkv, D, device="cuda", dtype=dt)
+        vl = torch.randn(nb, page, Hkv, D, device="cuda", dtype=dt)
+        btl = torch.randperm(nb, device="cuda").reshape(Bl, rows // page).int()
+        full_len = torch.full((Bl,), KV, dtype=torch.int32, device="cuda")
+        ll = P.kv_shard_lengths(full_len, rank, rows)
+        gathered = torch.empty(world, Bl * Hq, D + 1, dtype=torch.float32, device="cuda")
+        fn = lambda: P.decode_kv_sharded(ql, kl, vl, ll, btl, world=world, gathered=gathered)  # noqa: E731
+        ms = timed(fn, 30, 5, world)
+        nbytes = 2.0 * Bl * KV * Hkv * D * 2
+        emit(rank, {"bench": "long-context decode, KV axis sharded", "world": world, "kv": KV, "B": Bl, "Hq": Hq, "Hkv": Hkv,
+                    "ms": round(ms, 4), "aggregate_GBps": round(nbytes / ms / 1e6, 1),
+                    "per_gpu_GBps": round(nbytes / ms / 1e6 / world, 1), "collective": "1 all_gather of B*Hq*(D+1) fp32 per rank"})
+        del kl, vl
+        torch.cuda.empty_cache()
+    # head-sharded prefill S=16K (B=1, H=32, Hkv=8): strong scaling, no collective
+    S = 4096 if args.quick else 16384
+    qh = torch.randn(1, S, 32, D, device="cuda", dtype=dt)
+    kh = torch.randn(1, S, 8, D, device="cuda", dtype=dt)
+    vh = torch.randn(1, S, 8, D, device="cuda", dtype=dt)
+    for causal in (False, True):
+        ms = timed(lambda: P.prefill_sharded(qh, kh, vh, causal, rank=rank, world=world), 5, 2, world)
+        fl = 4.0 * 32 * S * S * D * (0.5 if causal else 1.0)
+        emit(rank, {"bench": "prefill sharded by kv-head, no collective", "world": world, "S": S, "H": 32, "Hkv": 8, "causal": causal,
+                    "ms": round(ms, 3), "aggregate_TFLOPs": round(fl / ms / 1e9, 1)})
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
