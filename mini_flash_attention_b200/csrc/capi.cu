@@ -11,6 +11,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 
 #include "../../include/mfa_b200.h"
 #include "kparams.h"
@@ -23,6 +24,8 @@ cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t s
 cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                            const PrefillKParams& p, bool is_bf16, int dpad, cudaStream_t stream);
 int prefill_rows_per_cta(int dpad);
+cudaError_t launch_prefill_pair(const CUtensorMap& tmK, const CUtensorMap& tmV, const PrefillKParams& p, bool is_bf16,
+                                cudaStream_t stream);
 }  // namespace mfa
 
 namespace {
@@ -128,14 +131,20 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
                      !mult8(p->o_batch_stride))))
         return fail(MFA_ERR_UNSUPPORTED, "row/head/batch strides must be multiples of 8 elements (16 bytes)");
     if (reinterpret_cast<uintptr_t>(p->o_ptr) & 15) return fail(MFA_ERR_UNSUPPORTED, "output must be 16-byte aligned");
+    if (reinterpret_cast<uintptr_t>(p->q_ptr) & 15) return fail(MFA_ERR_UNSUPPORTED, "q must be 16-byte aligned");
 
     const int D = p->head_dim;
     const int dpad = dpad_of(D);
     const bool bf16 = p->is_bf16 != 0;
 
+    // head_dim in (64, 128]: CTA-pair kernel (prefill_pair_sm100.cu); MFA_PREFILL_SINGLE=1 forces the single-CTA kernel
+    static const bool force_single = [] { const char* e = getenv("MFA_PREFILL_SINGLE"); return e && e[0] == '1'; }();
+    const bool use_pair = (dpad == 128) && !force_single;
+    const int kv_tile_box = use_pair ? 64 : mfa::kPrefillBlockN;
+
     CUtensorMap tmQ, tmK, tmV;
     const char* err;
-    {
+    if (!use_pair) {
         const uint64_t rows = varlen ? (uint64_t)p->total_q : (uint64_t)p->seqlen_q;
         if (rows == 0) return fail(MFA_ERR_INVALID_ARG, "q has no rows");
         const uint64_t dims[4] = {(uint64_t)D, rows, (uint64_t)p->heads, varlen ? 1ull : (uint64_t)p->batch};
@@ -143,11 +152,11 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
         const uint32_t box[4] = {64, (uint32_t)mfa::kPrefillBlockM, 1, 1};
         if ((err = mfa::encode_tmap_4d(&tmQ, p->q_ptr, bf16, dims, strides, box))) return fail(MFA_ERR_UNSUPPORTED, "q: %s", err);
     }
-    int kv_box_rows = mfa::kPrefillBlockN;
+    int kv_box_rows = kv_tile_box;
     if (paged) {
         if (p->page_block_size <= 0 || p->num_blocks <= 0 || p->max_blocks_per_seq <= 0)
             return fail(MFA_ERR_INVALID_ARG, "paged K/V needs page_block_size, num_blocks and max_blocks_per_seq");
-        kv_box_rows = gcd_int(p->page_block_size, mfa::kPrefillBlockN);
+        kv_box_rows = gcd_int(p->page_block_size, kv_tile_box);
         if (kv_box_rows < 8)
             return fail(MFA_ERR_UNSUPPORTED, "page_block_size must be a multiple of 8 (got %d)", p->page_block_size);
         if (!mult8(p->k_cache_block_stride) || !mult8(p->v_cache_block_stride))
@@ -164,12 +173,16 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
         const uint64_t dims[4] = {(uint64_t)D, rows, (uint64_t)p->kv_heads, varlen ? 1ull : (uint64_t)p->batch};
         const int64_t ks[4] = {1, p->k_row_stride, p->k_head_stride, varlen ? 0 : p->k_batch_stride};
         const int64_t vs[4] = {1, p->v_row_stride, p->v_head_stride, varlen ? 0 : p->v_batch_stride};
-        const uint32_t box[4] = {64, (uint32_t)mfa::kPrefillBlockN, 1, 1};
+        const uint32_t box[4] = {64, (uint32_t)kv_tile_box, 1, 1};
         if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k: %s", err);
         if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v: %s", err);
     }
 
     mfa::PrefillKParams kp{};
+    kp.q = p->q_ptr;
+    kp.q_batch_stride = p->q_batch_stride;
+    kp.q_head_stride = p->q_head_stride;
+    kp.q_row_stride = p->q_row_stride;
     kp.o = p->o_ptr;
     kp.o_batch_stride = p->o_batch_stride;
     kp.o_head_stride = p->o_head_stride;
@@ -196,7 +209,8 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     kp.lse = nullptr;
     kp.trace = g_trace;
 
-    cudaError_t e = mfa::launch_prefill(tmQ, tmK, tmV, kp, bf16, dpad, static_cast<cudaStream_t>(cuda_stream));
+    cudaError_t e = use_pair ? mfa::launch_prefill_pair(tmK, tmV, kp, bf16, static_cast<cudaStream_t>(cuda_stream))
+                             : mfa::launch_prefill(tmQ, tmK, tmV, kp, bf16, dpad, static_cast<cudaStream_t>(cuda_stream));
     if (e != cudaSuccess) return cuda_fail(e, "prefill launch");
     g_launches.fetch_add(1);
     return MFA_OK;
