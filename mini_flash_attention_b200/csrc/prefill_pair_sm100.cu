@@ -45,8 +45,13 @@
     do {                                                                                                  \
         if (tr_on && (it) < 64) p.trace[((role) * 64 + (it)) * 8 + (ev)] = clock64();                      \
     } while (0)
+#define MFA_CT(ev, val)                                                                                   \
+    do {                                                                                                  \
+        if (ct_on) p.trace[3 * 64 * 8 + blockIdx.x * 8 + (ev)] = (long long)(val);                          \
+    } while (0)
 #else
 #define MFA_TR(role, it, ev) do { } while (0)
+#define MFA_CT(ev, val) do { } while (0)
 #endif
 
 namespace mfa {
@@ -125,7 +130,14 @@ __device__ __forceinline__ uint64_t pair_exp2_poly2(uint64_t x2) {
     return f2_pack(r0, r1);
 }
 
-__device__ __forceinline__ void pair_bar_sync_softmax() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+// The two threads of a query row live in warps w and w + 4: a 64-thread named barrier per warp pair (ids 1-4).
+__device__ __forceinline__ void pair_bar_sync_rows(int warp_in_wg) {
+#ifdef MFA_PAIR_BAR256
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+#else
+    asm volatile("bar.sync %0, 64;" ::"r"(warp_in_wg + 1) : "memory");
+#endif
+}
 
 template <typename T>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
@@ -158,6 +170,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
     const int rank = (int)cluster_ctarank();
 #ifdef MFA_TRACE
     const bool tr_on = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp == 9 || (warp & 3) == 0);
+    // CTA lifetime stamps of the CTAs (x < 64, 0, gridDim.z / 2): steady state, not the first wave
+    const bool ct_on = p.trace && blockIdx.y == 0 && blockIdx.z == gridDim.z / 2 && blockIdx.x < 64 && threadIdx.x == 0;
+    MFA_CT(0, clock64());
+    MFA_CT(6, globaltimer_ns());
 #endif
 
     // ---- work item.  Causal: heaviest (largest m) pairs first.
@@ -206,6 +222,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
     cluster_sync();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    MFA_CT(1, clock64());
 
     if (warp == 8) {
         // ======================================================================= TMA producer (both CTAs)
@@ -289,7 +306,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
                     for (int r = rows_valid; r < kBN; ++r) *reinterpret_cast<uint32_t*>(dst + r * 128 + lane * 4) = 0u;
                     fence_proxy_async_smem();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive_leader(vfix_bar);
+                    if (lane == 0) mbar_arrive_leader_release(vfix_bar);
                 }
             }
         }
@@ -357,6 +374,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
                     tc_fence_after();
                     MFA_TR(2, j, 0);
                     issue_S(buf ^ 1, sK);
+                    MFA_TR(2, j, 4);
                 }
                 const int sV = it % kStages;
                 if (v_fix_last && j == n_tiles - 1) mbar_wait(vfix_bar, 0);   // zero-tailed V tile: signalled by both producers
@@ -365,6 +383,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
 #ifdef MFA_DBG_SLEEP
                 __nanosleep(50000);
 #endif
+                MFA_TR(2, j, 5);
                 mbar_wait(&p_lo[buf], pph);
                 tc_fence_after();
                 MFA_TR(2, j, 1);
@@ -416,6 +435,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
             mbar_wait(&s_full[buf], (uint32_t)(j >> 1) & 1u);
             tc_fence_after();
             MFA_TR(wg, j, 1);
+            if (j == 0) MFA_CT(2, clock64());
+#ifdef MFA_DBG_NOSOFTMAX
+            // perf experiment only (wrong results): no softmax work, P released at once -> pure TMA + MMA pipeline rate
+            if (j > 0) mbar_wait(o_full, (uint32_t)(j - 1) & 1u);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(wg == 0 ? &p_lo[buf] : &p_hi[buf]);
+            MFA_TR(wg, j, 4);
+            continue;
+#endif
             uint32_t su[64];   // this thread's half S row (fp32 bit patterns)
             tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&su[0]));
             tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&su[32]));
@@ -444,7 +473,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
             // exchange with the thread that owns the other 64 columns of this row
             float* xb = xchg + buf * 256;
             xb[wg * 128 + row_in_tile] = pmax;
-            pair_bar_sync_softmax();
+            pair_bar_sync_rows(warp & 3);
             const float tmax = fmaxf(pmax, xb[(wg ^ 1) * 128 + row_in_tile]);
             const float m_new = fmaxf(m_run, tmax);
             // lazy rescale: keep the stale max unless it grew by more than 2^8 (both threads of a row decide alike)
@@ -508,11 +537,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
             l_run = l_run * factor + ((sa + sb) + (sc + sd));
         }
 
+        MFA_CT(3, clock64());
         // ---- epilogue: (l_A + l_B), O / l -> out dtype -> global.  tcgen05.ld is warp-collective, so every lane
         // takes part in the TMEM loads; only the global stores are guarded by row < len_q.
         {
             lsum[wg * 128 + row_in_tile] = l_run;
-            pair_bar_sync_softmax();
+            pair_bar_sync_rows(warp & 3);
             const float l_tot = l_run + lsum[(wg ^ 1) * 128 + row_in_tile];
             T* orow = static_cast<T*>(p.o) + (int64_t)h * p.o_head_stride + wg * 64 +
                       (p.cu_seqlens_q ? (int64_t)(q_off + qrow) * p.o_row_stride
@@ -549,6 +579,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
         }
     }
 
+    if (warp < 8) MFA_CT(4, clock64());
     // ---- teardown: nobody may leave (or free TMEM) while the peer can still signal its barriers / read its smem
     tc_fence_before();
     cluster_sync();
@@ -556,6 +587,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
         tc_fence_after();
         tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
     }
+    MFA_CT(5, clock64());
+    MFA_CT(7, globaltimer_ns());
 }
 
 }  // namespace

@@ -398,6 +398,13 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             mbar_wait(&s_full[i], j & 1);
             tc_fence_after();
             MFA_TR(i, j, 1);
+#ifdef MFA_DBG_NOSOFTMAX
+            // perf experiment only (wrong results): pure TMA + MMA pipeline rate
+            tc_fence_before();
+            mbar_arrive(&p_lo[i]);
+            mbar_arrive(&p_hi[i]);
+            continue;
+#endif
             uint32_t su[128];   // this thread's S row (fp32 bit patterns)
 #pragma unroll
             for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&su[c * 32]));

@@ -291,7 +291,12 @@ __device__ __forceinline__ void cluster_sync() {
 __device__ __forceinline__ uint32_t leader_addr(const void* p) { return smem_u32(p) & kPeerBitMask; }
 
 // arrive (count 1) on the LEADER CTA's copy of `bar` (works from either CTA of the pair)
+// (plain form: a .release.cluster arrive compiles to MEMBAR.ALL.GPU + ERRBAR, ~2500 cycles per call)
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(leader_addr(bar)) : "memory");
+}
+// same with cluster-scope release semantics, for the rare hand-off of generic-proxy shared-memory writes
+__device__ __forceinline__ void mbar_arrive_leader_release(uint64_t* bar) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(leader_addr(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx_leader(uint64_t* bar, uint32_t bytes) {

@@ -36,7 +36,8 @@ __global__ void __launch_bounds__(128) umma_selftest2_kernel(const __grid_consta
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_tma + 2);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = kPair ? cluster_ctarank() : 0u;
-    const bool ts = (p.mode & 1) != 0;
+    const bool ts = (p.mode & 1) != 0 || p.mode >= 4;   // A from TMEM
+    const bool bk = p.mode >= 4;                        // modes 4/5: B is K-major (the S = Q K^T shape with Q in TMEM)
 
     if (threadIdx.x == 0) {
         mbar_init(bar_tma, kPair ? 2 : 1);
@@ -79,7 +80,14 @@ __global__ void __launch_bounds__(128) umma_selftest2_kernel(const __grid_consta
 
     if (threadIdx.x == 0) {
         // ---- loads: every CTA loads its own operand parts; completion is counted on the leader's barrier
-        if (!ts) {
+        if (bk) {
+            const uint32_t bytes = 2 * nb * 128;
+            if (kPair) mbar_arrive_expect_tx_leader(bar_tma, bytes); else mbar_arrive_expect_tx(bar_tma, bytes);
+            for (int s = 0; s < 2; ++s) {
+                if (kPair) tma_load_4d_pair(b_smem + s * nb * 128, &tmB, bar_tma, s * 64, (int)rank * 64, 0, 0);
+                else tma_load_4d(b_smem + s * nb * 128, &tmB, bar_tma, s * 64, 0, 0, 0);
+            }
+        } else if (!ts) {
             const uint32_t bytes = 2 * 16384 + 2 * nb * 128;
             if (kPair) mbar_arrive_expect_tx_leader(bar_tma, bytes); else mbar_arrive_expect_tx(bar_tma, bytes);
             for (int s = 0; s < 2; ++s) {
@@ -107,7 +115,7 @@ __global__ void __launch_bounds__(128) umma_selftest2_kernel(const __grid_consta
     if (warp == 0 && rank == 0) {
         mbar_wait(bar_tma, 0);
         tc_fence_after();
-        const uint32_t idesc = umma_idesc_f16(fmt, kPair ? 256 : 128, 128, 0, ts ? 1 : 0);
+        const uint32_t idesc = umma_idesc_f16(fmt, kPair ? 256 : 128, 128, 0, (ts && !bk) ? 1 : 0);
         const uint32_t a_addr = smem_u32(a_smem), b_addr = smem_u32(b_smem);
         const long long t0 = clock64();
         for (int rep = 0; rep < p.reps; ++rep) {
@@ -119,6 +127,10 @@ __global__ void __launch_bounds__(128) umma_selftest2_kernel(const __grid_consta
                         const uint64_t ad = umma_smem_desc(a_addr + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2);
                         const uint64_t bd = umma_smem_desc(b_addr + (ks >> 2) * nb * 128 + (ks & 3) * 32, 16, 1024, 2);
                         if (kPair) umma_ss_pair(tmem, ad, bd, idesc, acc); else umma_ss(tmem, ad, bd, idesc, acc);
+                    } else if (bk) {
+                        const uint64_t bd = umma_smem_desc(b_addr + (ks >> 2) * nb * 128 + (ks & 3) * 32, 16, 1024, 2);
+                        if (kPair) umma_ts_pair(tmem, tmem + 256 + ks * 8, bd, idesc, acc);
+                        else umma_ts(tmem, tmem + 256 + ks * 8, bd, idesc, acc);
                     } else {
                         const uint64_t bd = umma_smem_desc(b_addr + ks * 2048, 16384, 1024, 2);
                         if (kPair) umma_ts_pair(tmem, tmem + 256 + ks * 8, bd, idesc, acc);
@@ -161,15 +173,16 @@ __global__ void __launch_bounds__(128) umma_selftest2_kernel(const __grid_consta
 extern "C" int mfa_selftest_umma2(int mode, const void* a, const void* b, float* d, int is_bf16, int reps,
                                   long long* cycles, void* cuda_stream) {
     using namespace mfa;
-    if (mode < 0 || mode > 3 || !a || !b || !d || reps < 1) return MFA_ERR_INVALID_ARG;
-    const bool pair = mode < 2;
-    const bool ts = (mode & 1) != 0;
+    if (mode < 0 || mode > 5 || !a || !b || !d || reps < 1) return MFA_ERR_INVALID_ARG;
+    const bool pair = mode < 2 || mode == 4;
+    const bool bk = mode >= 4;
+    const bool ts = (mode & 1) != 0 || bk;
     CUtensorMap tmA, tmB;
     const uint64_t dimsA[4] = {128, 256, 1, 1};
     const uint64_t dimsB[4] = {128, 128, 1, 1};
     const int64_t st[4] = {1, 128, 0, 0};
     const uint32_t boxA[4] = {64, 128, 1, 1};
-    const uint32_t boxB[4] = {64, (ts || !pair) ? 128u : 64u, 1, 1};
+    const uint32_t boxB[4] = {64, ((ts && !bk) || !pair) ? 128u : 64u, 1, 1};
     if (!ts && encode_tmap_4d(&tmA, a, is_bf16, dimsA, st, boxA)) return MFA_ERR_UNSUPPORTED;
     if (encode_tmap_4d(&tmB, b, is_bf16, dimsB, st, boxB)) return MFA_ERR_UNSUPPORTED;
     if (ts) tmA = tmB;

@@ -10,18 +10,20 @@ from mini_flash_attention_b200 import _lib
 S = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 B, H, D = 48, 24, 128
 q, k, v = (torch.randn(B, S, H, D, device="cuda", dtype=torch.bfloat16) for _ in range(3))
-buf = torch.zeros(3 * 64 * 8, dtype=torch.int64, device="cuda")
+buf = torch.zeros(3 * 64 * 8 + 64 * 8, dtype=torch.int64, device="cuda")
 for _ in range(3):
     mfa.flash_attn_func(q, k, v)
 _lib.load().mfa_debug_set_trace(buf.data_ptr())
 mfa.flash_attn_func(q, k, v)
 torch.cuda.synchronize()
 _lib.load().mfa_debug_set_trace(None)
-t = buf.cpu().view(3, 64, 8)
+ct = buf.cpu()[3 * 64 * 8:].view(64, 8)
+t = buf.cpu()[:3 * 64 * 8].view(3, 64, 8)
 t0 = int(t[t > 0].min())
 r = lambda x: int(x) - t0 if int(x) > 0 else -1
 print("softmax events: 0 loop top, 1 S ready, 2 S in regs, 3 max/rescale done, 4 P_lo released, 5 P_hi released")
-print("mma events: 0 K/V ready, 1 p_lo0 seen, 2 p_hi0 seen, 3 PV0+S0 issued, 4 p_lo1 seen, 5 p_hi1 seen, 6 PV1+S1 issued")
+print("mma events (single): 0 K/V ready, 1 p_lo0 seen, 2 p_hi0 seen, 3 PV0+S0 issued, 4 p_lo1 seen, 5 p_hi1 seen, 6 PV1+S1 issued")
+print("mma events (pair): 0 K(j+1) ready, 4 S(j+1) issued, 5 V(j) ready, 1 p_lo seen, 2 p_hi seen (PV lo issued), 3 PV hi issued")
 n = min(S // 128, 64)
 for j in list(range(0, 6)) + list(range(n - 3, n)):
     print(f"j={j:2d} WG0 {[r(x) for x in t[0, j, :6]]}  WG1 {[r(x) for x in t[1, j, :6]]}  MMA {[r(x) for x in t[2, j, :7]]}")
@@ -35,3 +37,12 @@ for role in (0, 1):
     seg = [[int(t[role, j, e + 1] - t[role, j, e]) for j in range(4, n - 1)] for e in range(1, 5)]
     print("WG", role, "busy median", statistics.median(busy), "wait-for-S median", statistics.median(wait),
           "segments ld/max/half0/half1", [statistics.median(s) for s in seg])
+
+if int(ct[:, 0].max()) > 0:
+    print("CTA lifetime (pair kernel; CTAs (x,0,B/2)): cycles entry->setup, ->first S, ->loop end, ->epilogue end, ->exit; wall ns; MHz")
+    for x in range(0, 64):
+        if int(ct[x, 0]) == 0:
+            continue
+        c = [int(v) for v in ct[x]]
+        ns = c[7] - c[6]
+        print(f"  x={x:2d} setup {c[1]-c[0]:6d} firstS {c[2]-c[0]:6d} loop_end {c[3]-c[0]:7d} epi {c[4]-c[0]:7d} exit {c[5]-c[0]:7d}  wall {ns:7d} ns  {1000.0*(c[5]-c[0])/max(ns,1):6.0f} MHz  start@{c[6] - int(ct[:,6][ct[:,6]>0].min()):8d} ns")

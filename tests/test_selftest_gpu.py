@@ -25,13 +25,13 @@ def test_umma_tile(mfa_lib, mode, kdim, ncols, bf16):
     assert (d - ref).abs().max().item() < 1e-3
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 5])
 @pytest.mark.parametrize("bf16", [False, True])
 def test_umma_pair_tile(mfa_lib, mode, bf16):
     """CTA-pair (cta_group::2) operand split conventions: A/P rows per CTA, B rows (SS) or head-dim columns (TS) per CTA."""
     torch.manual_seed(1)
     dt = torch.bfloat16 if bf16 else torch.float16
-    if mode in (0, 2):
+    if mode in (0, 2, 4, 5):
         a = torch.randn(256, 128, device="cuda", dtype=dt)
         b = torch.randn(128, 128, device="cuda", dtype=dt)
         ref = a.float() @ b.float().t()
@@ -44,5 +44,5 @@ def test_umma_pair_tile(mfa_lib, mode, bf16):
     rc = mfa_lib.mfa_selftest_umma2(mode, a.data_ptr(), b.data_ptr(), d.data_ptr(), int(bf16), 1, cyc.data_ptr(), None)
     torch.cuda.synchronize()
     assert rc == 0
-    rows = 256 if mode < 2 else 128
+    rows = 256 if mode in (0, 1, 4) else 128
     assert (d[:rows] - ref[:rows]).abs().max().item() < 1e-3
