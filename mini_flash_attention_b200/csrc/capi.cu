@@ -24,8 +24,8 @@ cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t s
 cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                            const PrefillKParams& p, bool is_bf16, int dpad, cudaStream_t stream);
 int prefill_rows_per_cta(int dpad);
-cudaError_t launch_prefill_pair(const CUtensorMap& tmK, const CUtensorMap& tmV, const PrefillKParams& p, bool is_bf16,
-                                cudaStream_t stream);
+cudaError_t launch_prefill_pair(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                                const PrefillKParams& p, bool is_bf16, cudaStream_t stream);
 }  // namespace mfa
 
 namespace {
@@ -144,7 +144,7 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
 
     CUtensorMap tmQ, tmK, tmV;
     const char* err;
-    if (!use_pair) {
+    {
         const uint64_t rows = varlen ? (uint64_t)p->total_q : (uint64_t)p->seqlen_q;
         if (rows == 0) return fail(MFA_ERR_INVALID_ARG, "q has no rows");
         const uint64_t dims[4] = {(uint64_t)D, rows, (uint64_t)p->heads, varlen ? 1ull : (uint64_t)p->batch};
@@ -209,7 +209,7 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     kp.lse = nullptr;
     kp.trace = g_trace;
 
-    cudaError_t e = use_pair ? mfa::launch_prefill_pair(tmK, tmV, kp, bf16, static_cast<cudaStream_t>(cuda_stream))
+    cudaError_t e = use_pair ? mfa::launch_prefill_pair(tmQ, tmK, tmV, kp, bf16, static_cast<cudaStream_t>(cuda_stream))
                              : mfa::launch_prefill(tmQ, tmK, tmV, kp, bf16, dpad, static_cast<cudaStream_t>(cuda_stream));
     if (e != cudaSuccess) return cuda_fail(e, "prefill launch");
     g_launches.fetch_add(1);

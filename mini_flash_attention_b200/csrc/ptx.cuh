@@ -60,15 +60,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// Wait until the phase with the given parity has completed.
+// Wait until the phase with the given parity has completed.  The watchdog clock (%globaltimer, a slow shared
+// resource) is only read every 4096 failed polls, so that spinning warps do not slow the rest of the SM down.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
-    const uint64_t t0 = globaltimer_ns();
+    uint32_t spins = 0;
+    uint64_t t0 = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (globaltimer_ns() - t0 > MFA_WATCHDOG_NS) {
-            printf("mfa: mbarrier watchdog block(%d,%d,%d) thread %d bar@%u parity %u\n", blockIdx.x, blockIdx.y,
-                   blockIdx.z, threadIdx.x, smem_u32(bar), parity);
-            __trap();
+        if ((++spins & 0xFFFu) == 0) {
+            const uint64_t t = globaltimer_ns();
+            if (t0 == 0) {
+                t0 = t;
+            } else if (t - t0 > MFA_WATCHDOG_NS) {
+                printf("mfa: mbarrier watchdog block(%d,%d,%d) thread %d bar@%u parity %u\n", blockIdx.x, blockIdx.y,
+                       blockIdx.z, threadIdx.x, smem_u32(bar), parity);
+                __trap();
+            }
         }
     }
 }

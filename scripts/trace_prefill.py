@@ -10,14 +10,15 @@ from mini_flash_attention_b200 import _lib
 S = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 B, H, D = 48, 24, 128
 q, k, v = (torch.randn(B, S, H, D, device="cuda", dtype=torch.bfloat16) for _ in range(3))
-buf = torch.zeros(3 * 64 * 8 + 64 * 8, dtype=torch.int64, device="cuda")
+buf = torch.zeros(4 * 64 * 8 + 64 * 8, dtype=torch.int64, device="cuda")
 for _ in range(3):
     mfa.flash_attn_func(q, k, v)
 _lib.load().mfa_debug_set_trace(buf.data_ptr())
 mfa.flash_attn_func(q, k, v)
 torch.cuda.synchronize()
 _lib.load().mfa_debug_set_trace(None)
-ct = buf.cpu()[3 * 64 * 8:].view(64, 8)
+ct = buf.cpu()[4 * 64 * 8:].view(64, 8)
+pr = buf.cpu()[3 * 64 * 8:4 * 64 * 8].view(64, 8)
 t = buf.cpu()[:3 * 64 * 8].view(3, 64, 8)
 t0 = int(t[t > 0].min())
 r = lambda x: int(x) - t0 if int(x) > 0 else -1
@@ -38,6 +39,9 @@ for role in (0, 1):
     print("WG", role, "busy median", statistics.median(busy), "wait-for-S median", statistics.median(wait),
           "segments ld/max/half0/half1", [statistics.median(s) for s in seg])
 
+if int(pr[:, 0].max()) > 0:
+    print("producer (pair kernel): load index, what, t(before empty-wait), t(issued)")
+    print("   " + "  ".join(f"{i}:{'V' if int(pr[i,2])>=1000 else 'K'}{int(pr[i,2])%1000}@{r(pr[i,0])}/{r(pr[i,1])}" for i in range(24)))
 if int(ct[:, 0].max()) > 0:
     print("CTA lifetime (pair kernel; CTAs (x,0,B/2)): cycles entry->setup, ->first S, ->loop end, ->epilogue end, ->exit; wall ns; MHz")
     for x in range(0, 64):
