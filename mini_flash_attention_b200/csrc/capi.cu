@@ -32,6 +32,11 @@ namespace {
 
 thread_local char g_err[512] = "";
 long long* g_trace = nullptr;   // tuning aid, see mfa_debug_set_trace
+static int initial_prefill_impl() {
+    const char* e = getenv("MFA_PREFILL_IMPL");
+    return (e && strcmp(e, "pair") == 0) ? 1 : 0;
+}
+std::atomic<int> g_prefill_impl{initial_prefill_impl()};   // 0 = single-CTA kernel, 1 = CTA-pair kernel (head_dim in (64,128])
 std::atomic<uint64_t> g_launches{0};
 
 int fail(int code, const char* fmt, ...) {
@@ -105,6 +110,7 @@ extern "C" {
 
 int mfa_abi_version(void) { return MFA_B200_ABI_VERSION; }
 void mfa_debug_set_trace(void* device_buffer) { g_trace = static_cast<long long*>(device_buffer); }
+void mfa_debug_set_prefill_impl(int impl) { g_prefill_impl.store(impl == 1 ? 1 : 0); }
 const char* mfa_last_error(void) { return g_err; }
 uint64_t mfa_launch_count(void) { return g_launches.load(); }
 
@@ -137,9 +143,9 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     const int dpad = dpad_of(D);
     const bool bf16 = p->is_bf16 != 0;
 
-    // head_dim in (64, 128]: CTA-pair kernel (prefill_pair_sm100.cu); MFA_PREFILL_SINGLE=1 forces the single-CTA kernel
-    static const bool force_single = [] { const char* e = getenv("MFA_PREFILL_SINGLE"); return e && e[0] == '1'; }();
-    const bool use_pair = (dpad == 128) && !force_single;
+    // head_dim in (64, 128] has two kernels: the single-CTA one (prefill_sm100.cu, default: faster today) and the
+    // CTA-pair one (prefill_pair_sm100.cu; MFA_PREFILL_IMPL=pair or mfa_debug_set_prefill_impl(1) selects it).
+    const bool use_pair = (dpad == 128) && (g_prefill_impl.load() == 1);
     const int kv_tile_box = use_pair ? 64 : mfa::kPrefillBlockN;
 
     CUtensorMap tmQ, tmK, tmV;

@@ -461,6 +461,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
             tc_fence_after();
             MFA_TR(wg, j, 1);
             if (j == 0) MFA_CT(2, clock64());
+#ifdef MFA_DBG_NOSOFTMAX
+            // perf experiment only (wrong results): no softmax work -> pure TMA + MMA pipeline rate
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(&s_free[buf]);
+            if (j > 1) mbar_wait(&o_full[j & 1], (uint32_t)((j - 2) >> 1) & 1u);
+            if (lane == 0) { mbar_arrive_leader(&p_lo[buf]); mbar_arrive_leader(&p_hi[buf]); }
+            if (j > 0) mbar_wait(&o_full[(j - 1) & 1], (uint32_t)((j - 1) >> 1) & 1u);
+            continue;
+#endif
             uint32_t su[128];   // this thread's S row (fp32 bit patterns)
 #pragma unroll
             for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&su[c * 32]));

@@ -35,7 +35,7 @@
 #include "ptx.cuh"
 
 #ifndef MFA_POLY_MASK
-#define MFA_POLY_MASK 0xAu   // pairs 1 and 3 of every 4 -> half of the exponentials off the MUFU
+#define MFA_POLY_MASK 0x8u   // pair 3 of every 4 -> a quarter of the exponentials off the MUFU (measured best)
 #endif
 
 #ifdef MFA_TRACE
@@ -216,14 +216,16 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
       asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     if (warp == 8) {
         // ======================================================================= TMA producer
-        if (lane == 0) {
+        // Warp-uniform control flow with one ELECTED lane issuing (see the MMA warp): under a divergent
+        // `if (lane == 0)` ptxas cannot keep the TMA operands in uniform registers.
+        if (elect_one()) {
             prefetch_tensormap(&tmQ);
             prefetch_tensormap(&tmK);
             prefetch_tensormap(&tmV);
         }
         const int q_row_coord = p.cu_seqlens_q ? (q_off + m0) : m0;
         const int q_b_coord = p.cu_seqlens_q ? 0 : b;
-        if (lane == 0) {
+        if (elect_one()) {
 #pragma unroll
             for (int i = 0; i < kNQ; ++i) {
                 if (n_i[i] > 0) {
@@ -253,8 +255,8 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 uint8_t* dst = ring + s * Cfg::kKVTileBytes;
                 const bool fix = kv && need_tail_fix && rows_valid < kBN;
                 uint64_t* bar = fix ? tail_bar : &kv_full[s];
-                if (lane == 0) {
-                    mbar_wait(&kv_empty[s], ph ^ 1);
+                mbar_wait(&kv_empty[s], ph ^ 1);
+                if (elect_one()) {
                     if (bt) {
                         const int nchunks = (rows_valid + p.kv_box_rows - 1) / p.kv_box_rows;
                         const int chunk_bytes = p.kv_box_rows * 128;
@@ -277,6 +279,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                                         packed_k ? 0 : b);
                     }
                 }
+                __syncwarp();
                 if (fix) {
                     // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
                     mbar_wait(tail_bar, tail_phase);

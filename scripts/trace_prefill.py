@@ -42,6 +42,8 @@ for role in (0, 1):
 if int(pr[:, 0].max()) > 0:
     print("producer (pair kernel): load index, what, t(before empty-wait), t(issued)")
     print("   " + "  ".join(f"{i}:{'V' if int(pr[i,2])>=1000 else 'K'}{int(pr[i,2])%1000}@{r(pr[i,0])}/{r(pr[i,1])}" for i in range(24)))
+    print("   K loads: elect-block entry / after expect_tx / after TMA 1 / after TMA 2")
+    print("   " + "  ".join(f"{i}:{r(pr[i,3])}/{r(pr[i,4])}/{r(pr[i,5])}/{r(pr[i,6])}" for i in range(16) if int(pr[i,2]) < 1000))
 if int(ct[:, 0].max()) > 0:
     print("CTA lifetime (pair kernel; CTAs (x,0,B/2)): cycles entry->setup, ->first S, ->loop end, ->epilogue end, ->exit; wall ns; MHz")
     for x in range(0, 64):
