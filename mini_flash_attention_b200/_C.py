@@ -299,3 +299,55 @@ def combine_partials(packed: torch.Tensor, out_dtype: torch.dtype, return_lse: b
                                                     lse.data_ptr() if lse is not None else None,
                                                     _stream_ptr(packed.device)), "mfa_combine_partials")
     return (out, lse) if return_lse else out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Compiled host boundary.  csrc/torch_shim.cpp holds the same validation / allocation / parameter fill in C++ (a torch
+# extension module linked against libmfa_b200.so, built in-tree by build.build_shim()); when it is present the three
+# entry points and decode_partial dispatch to it, which takes the per-call host cost from ~29 us (ctypes struct fill
+# in Python) to a few us.  The Python bodies above stay as the same logic over the same C-ABI: used when the module
+# has not been built, when MFA_B200_SHIM=py, or when MFA_B200_LIB points at another build of the library.
+# Either way the arithmetic is libmfa_b200.so's CUDA kernels; neither path has a CPU fallback.
+# ---------------------------------------------------------------------------------------------------------------
+import os as _os
+
+_py_forward = mini_flash_attention_forward
+_py_varlen_forward = mini_flash_attention_varlen_forward
+_py_with_kvcache = mini_flash_attention_with_kvcache
+_py_decode_partial = decode_partial
+SHIM = "python"
+_shim_error = None
+
+
+def _load_compiled_shim():
+    if _os.environ.get("MFA_B200_SHIM", "").lower() in ("py", "python") or _os.environ.get("MFA_B200_LIB"):
+        return None
+    try:
+        from . import _mfa_torch_shim as m  # noqa: WPS433
+    except ImportError as e:
+        global _shim_error
+        _shim_error = e
+        if _os.environ.get("MFA_B200_SHIM", "").lower() in ("cpp", "compiled"):
+            raise
+        return None
+    return m
+
+
+_shim = _load_compiled_shim()
+if _shim is not None:
+    SHIM = "compiled"
+    mini_flash_attention_forward = _shim.mini_flash_attention_forward
+    mini_flash_attention_varlen_forward = _shim.mini_flash_attention_varlen_forward
+
+    def mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits=0):
+        if isinstance(cache_seqlens, int):  # superset (quirk Q5): broadcast an int
+            cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
+        return _shim.mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)
+
+    def decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits=0):
+        if isinstance(cache_seqlens, int):
+            cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
+        return _shim.decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
+
+    mini_flash_attention_with_kvcache.__doc__ = _py_with_kvcache.__doc__
+    decode_partial.__doc__ = _py_decode_partial.__doc__

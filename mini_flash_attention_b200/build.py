@@ -100,6 +100,47 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB_PATH
 
 
+SHIM_NAME = "_mfa_torch_shim"
+SHIM_SRC = os.path.join(CSRC, "torch_shim.cpp")
+
+
+def shim_path() -> str:
+    import sysconfig
+    return os.path.join(PKG_DIR, SHIM_NAME + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_shim(force: bool = False, verbose: bool = False) -> str:
+    """Compiled host boundary (csrc/torch_shim.cpp): a torch extension module over libmfa_b200.so, built with plain
+    g++ against this interpreter's torch headers.  Depends on the torch build, so it is rebuilt when torch changes."""
+    import sysconfig
+    import torch
+    from torch.utils import cpp_extension as ce
+    out = shim_path()
+    lib = build(force=False, verbose=verbose)
+    deps = [SHIM_SRC, os.path.join(REPO, "include", "mfa_b200.h"), os.path.abspath(__file__), torch.__file__]
+    if not force and not _stale(out, deps):
+        return out
+    t0 = time.time()
+    incs = ce.include_paths("cuda") + [sysconfig.get_paths()["include"]]
+    torch_lib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    cuda_lib = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "lib64")
+    cmd = (["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-fvisibility=hidden", "-Wno-attributes",
+            f"-DTORCH_EXTENSION_NAME={SHIM_NAME}", "-DTORCH_API_INCLUDE_EXTENSION_H",
+            f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}"]
+           + [f"-I{i}" for i in incs] + [SHIM_SRC, "-o", out]
+           + [f"-L{PKG_DIR}", "-lmfa_b200", f"-L{torch_lib}", "-ltorch_python", "-ltorch", "-ltorch_cpu", "-ltorch_cuda",
+              "-lc10", "-lc10_cuda", f"-L{cuda_lib}", "-lcudart",
+              "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{torch_lib}", "-Wl,--no-as-needed"])
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("torch shim build failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(f"[mfa_b200] built {out} in {time.time() - t0:.1f}s")
+    return out
+
+
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose="--verbose" in sys.argv or "-v" in sys.argv)
     print(LIB_PATH)
+    if "--no-shim" not in sys.argv:
+        print(build_shim(force="--force" in sys.argv, verbose="--verbose" in sys.argv or "-v" in sys.argv))

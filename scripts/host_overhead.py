@@ -6,6 +6,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 import mini_flash_attention as mfa
+from mini_flash_attention_b200 import _C
+print("host shim:", _C.SHIM)
 
 def bench(name, fn, n=200):
     for _ in range(10):
