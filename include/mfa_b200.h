@@ -84,7 +84,8 @@ typedef struct mfa_params {
     /* decode -- flash.h:64-72 */
     const int32_t* seqlens_k;   /* (batch) int32 device; NULL => every row attends to seqlen_k keys */
     int32_t num_splits;         /* <= 0: heuristic ; clamped to the number of 64-row KV blocks (api.cpp:320-327) */
-    float*  softmax_lse_ptr;    /* optional (batch, heads) fp32 natural-log LSE output, may be NULL */
+    float*  softmax_lse_ptr;    /* optional fp32 natural-log LSE output, may be NULL (-inf for rows that see no key):
+                                 * decode (batch, heads); prefill fixed (batch, heads, seqlen_q), packed (heads, total_q) */
 
     /* multi-GPU KV-sharded decode: when partial_out != 0 the decode writes a NORMALISED fp32
      * partial O (batch, heads, head_dim) to o_ptr instead of fp16/bf16, and softmax_lse_ptr

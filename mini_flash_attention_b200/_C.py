@@ -70,8 +70,9 @@ def _i32_ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
-def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, window_size_right):
-    """Fixed-length prefill.  q (B,Sq,H,D); k, v (B,Sk,Hkv,D); returns (B,Sq,H,D).  api.cpp:113-186."""
+def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, window_size_right, _want_lse=False):
+    """Fixed-length prefill.  q (B,Sq,H,D); k, v (B,Sk,Hkv,D); returns (B,Sq,H,D).  api.cpp:113-186.
+    With _want_lse (the `_lse` entry point) also the natural-log LSE (B,H,Sq) fp32."""
     _check_qkv(q, k, v)
     _check(q.dim() == 4 and k.dim() == 4 and v.dim() == 4, "q, k, v must be 4-D (batch, seqlen, heads, head_dim)")
     batch, seqlen_q, num_heads, head_dim = q.shape
@@ -88,10 +89,11 @@ def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, wind
         _check(out.dtype == q.dtype and out.is_cuda, "out must match q's dtype and device")
     else:
         out = torch.empty_like(q)
+    lse = torch.empty(batch, num_heads, seqlen_q, dtype=torch.float32, device=q.device) if _want_lse else None
     if batch == 0 or seqlen_q == 0 or num_heads == 0:
-        return out
+        return (out, lse) if _want_lse else out
     if seqlen_k == 0:
-        return out.zero_()
+        return (out.zero_(), lse.fill_(float("-inf"))) if _want_lse else out.zero_()
     qc, kc, vc = _tma_ready(q), _tma_ready(k), _tma_ready(v)
     oc = out if _tma_ok(out) else torch.empty(out.shape, dtype=out.dtype, device=out.device)
 
@@ -106,15 +108,17 @@ def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, wind
     P.heads, P.kv_heads, P.batch = num_heads, kv_num_heads, batch
     P.seqlen_q, P.seqlen_k, P.head_dim = seqlen_q, seqlen_k, head_dim
     P.is_bf16 = int(q.dtype == torch.bfloat16)
+    if _want_lse:
+        P.softmax_lse_ptr = lse.data_ptr()
     with torch.cuda.device(q.device):  # api.cpp:123
         _lib.check(_lib.load().mfa_prefill_fwd(ctypes.byref(P), _stream_ptr(q.device)), "mfa_prefill_fwd")
     if oc is not out:
         out.copy_(oc)
-    return out
+    return (out, lse) if _want_lse else out
 
 
 def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal,
-                                        window_size_left, window_size_right, block_table):
+                                        window_size_left, window_size_right, block_table, _want_lse=False):
     """Packed variable-length prefill, optionally with paged K/V.  api.cpp:189-267.
 
     q (total_q,H,D); k, v (total_k,Hkv,D) or, with block_table (batch,max_blocks) int32,
@@ -130,8 +134,10 @@ def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max
     kv_num_heads = k.shape[-2]
     _check_head_dim(head_dim, num_heads, kv_num_heads)
     out = torch.empty_like(q)
+    # LSE in flash-attn's packed layout (H, total_q); rows past cu_seqlens_q[batch] are not written by the kernel
+    lse = torch.full((num_heads, total_q), float("-inf"), dtype=torch.float32, device=q.device) if _want_lse else None
     if batch == 0 or total_q == 0 or num_heads == 0:
-        return out
+        return (out, lse) if _want_lse else out
     cu_q, cu_k = cu_seqlens_q.contiguous(), cu_seqlens_k.contiguous()
 
     P = MfaParams()
@@ -158,7 +164,7 @@ def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max
         _check(tuple(k.shape) == (total_k, kv_num_heads, head_dim), "k must have shape (total_k, kv_num_heads, head_dim)")
         _check(tuple(v.shape) == (total_k, kv_num_heads, head_dim), "v must have shape (total_k, kv_num_heads, head_dim)")
         if total_k == 0:
-            return out.zero_()
+            return (out.zero_(), lse) if _want_lse else out.zero_()
         kc, vc = _tma_ready(k), _tma_ready(v)
         P.total_k = total_k
         P.k_row_stride, P.k_head_stride = kc.stride(0), kc.stride(1)
@@ -174,9 +180,11 @@ def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max
     P.is_bf16 = int(q.dtype == torch.bfloat16)
     P.cu_seqlens_q, P.cu_seqlens_k = cu_q.data_ptr(), cu_k.data_ptr()
     P.total_q = total_q
+    if _want_lse:
+        P.softmax_lse_ptr = lse.data_ptr()
     with torch.cuda.device(q.device):
         _lib.check(_lib.load().mfa_prefill_fwd(ctypes.byref(P), _stream_ptr(q.device)), "mfa_prefill_fwd")
-    return out
+    return (out, lse) if _want_lse else out
 
 
 def _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits):
@@ -237,19 +245,23 @@ def _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits):
 
 
 def mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens: Optional[Union[int, torch.Tensor]],
-                                      block_table, causal, num_splits=0):
+                                      block_table, causal, num_splits=0, _want_lse=False):
     """q_len == 1 decode over a contiguous or paged KV cache.  api.cpp:343-446.
     `causal` is accepted and ignored exactly like the reference (api.cpp:349, quirk Q10)."""
     P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
     out = torch.empty_like(q)  # api.cpp:405
+    # (B, H, 1) fp32: the tensor the reference allocates and drops (api.cpp:436-437)
+    lse = torch.empty(q.shape[0], q.shape[2], 1, dtype=torch.float32, device=q.device) if _want_lse else None
     if q.numel() == 0:
-        return out
+        return (out, lse) if _want_lse else out
     if P.seqlen_k == 0:
-        return out.zero_()
+        return (out.zero_(), lse.fill_(float("-inf"))) if _want_lse else out.zero_()
     oc = out if (out.data_ptr() % 8 == 0 and out.stride(0) % 4 == 0 and out.stride(2) % 4 == 0) else \
         torch.empty(out.shape, dtype=out.dtype, device=out.device)
     P.o_ptr = oc.data_ptr()
     P.o_batch_stride, P.o_row_stride, P.o_head_stride = oc.stride(0), oc.stride(1), oc.stride(2)
+    if _want_lse:
+        P.softmax_lse_ptr = lse.data_ptr()
     lib = _lib.load()
     with torch.cuda.device(q.device):
         splits = lib.mfa_decode_num_splits(ctypes.byref(P))
@@ -261,7 +273,7 @@ def mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens: Option
                                       _stream_ptr(q.device)), "mfa_decode_fwd")
     if oc is not out:
         out.copy_(oc)
-    return out
+    return (out, lse) if _want_lse else out
 
 
 def decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits=0):
@@ -315,6 +327,26 @@ _py_forward = mini_flash_attention_forward
 _py_varlen_forward = mini_flash_attention_varlen_forward
 _py_with_kvcache = mini_flash_attention_with_kvcache
 _py_decode_partial = decode_partial
+
+
+# (out, lse) variants -- SURVEY 8f row 1: the LSE the reference computes and drops, exposed
+def mini_flash_attention_forward_lse(q, k, v, out, is_causal, window_size_left, window_size_right):
+    return _py_forward(q, k, v, out, is_causal, window_size_left, window_size_right, _want_lse=True)
+
+
+def mini_flash_attention_varlen_forward_lse(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal,
+                                            window_size_left, window_size_right, block_table):
+    return _py_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal,
+                              window_size_left, window_size_right, block_table, _want_lse=True)
+
+
+def mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits=0):
+    return _py_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits, _want_lse=True)
+
+
+_py_forward_lse = mini_flash_attention_forward_lse
+_py_varlen_forward_lse = mini_flash_attention_varlen_forward_lse
+_py_with_kvcache_lse = mini_flash_attention_with_kvcache_lse
 SHIM = "python"
 _shim_error = None
 
@@ -322,13 +354,16 @@ _shim_error = None
 def _load_compiled_shim():
     if _os.environ.get("MFA_B200_SHIM", "").lower() in ("py", "python") or _os.environ.get("MFA_B200_LIB"):
         return None
+    global _shim_error
     try:
         from . import _mfa_torch_shim as m  # noqa: WPS433
     except ImportError as e:
-        global _shim_error
         _shim_error = e
         if _os.environ.get("MFA_B200_SHIM", "").lower() in ("cpp", "compiled"):
             raise
+        return None
+    if not hasattr(m, "mini_flash_attention_with_kvcache_lse"):   # built from an older torch_shim.cpp: rebuild with build()
+        _shim_error = ImportError("stale _mfa_torch_shim module (run python -m mini_flash_attention_b200.build)")
         return None
     return m
 
@@ -348,6 +383,14 @@ if _shim is not None:
         if isinstance(cache_seqlens, int):
             cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
         return _shim.decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
+
+    mini_flash_attention_forward_lse = _shim.mini_flash_attention_forward_lse
+    mini_flash_attention_varlen_forward_lse = _shim.mini_flash_attention_varlen_forward_lse
+
+    def mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits=0):
+        if isinstance(cache_seqlens, int):
+            cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
+        return _shim.mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)
 
     mini_flash_attention_with_kvcache.__doc__ = _py_with_kvcache.__doc__
     decode_partial.__doc__ = _py_decode_partial.__doc__

@@ -212,7 +212,9 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     kp.num_m_blocks = (p->seqlen_q + rows_per_cta - 1) / rows_per_cta;
     kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);   // api.cpp:99
     kp.scale_log2 = kp.scale * 1.4426950408889634f;                                      // api.cpp:100
-    kp.lse = nullptr;
+    kp.lse = p->softmax_lse_ptr;   // (B, H, Sq) fixed / (H, total_q) packed, contiguous
+    kp.lse_batch_stride = varlen ? 0 : (int64_t)p->heads * p->seqlen_q;
+    kp.lse_head_stride = varlen ? (int64_t)p->total_q : (int64_t)p->seqlen_q;
     kp.trace = g_trace;
 
     cudaError_t e = use_pair ? mfa::launch_prefill_pair(tmQ, tmK, tmV, kp, bf16, static_cast<cudaStream_t>(cuda_stream))

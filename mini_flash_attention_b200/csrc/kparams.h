@@ -65,7 +65,8 @@ struct PrefillKParams {
     int32_t is_causal;
     int32_t num_m_blocks;          // ceil(seqlen_q / 256)
     float scale, scale_log2;
-    float* lse;                    // optional (B, H, Sq) / (H, total_q): not exposed yet
+    float* lse;                    // optional natural-log LSE: (B, H, Sq) fixed / (H, total_q) packed; -inf for empty rows
+    int64_t lse_batch_stride, lse_head_stride;   // elements; the row index is q_off + row (q_off = 0 when fixed)
     long long* trace;              // MFA_TRACE builds only: clock64() stamps of CTA (0,0,0), [role][iter][8]
 };
 

@@ -597,6 +597,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
                     pair_bar_sync(1 + (last & 1) * 4 + wq);
                     const float m_fin = xm[(last & 1) * 128 + row_in_tile];
                     if (m_ref != m_fin) l_part = (m_ref == -INFINITY) ? 0.f : l_part * exp2f((m_ref - m_fin) * c2);
+                    m_ref = m_fin;
                 }
             }
             lsum[wg * 128 + row_in_tile] = l_part;
@@ -610,6 +611,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPrefillThreads, 1)
                 tc_fence_after();
             }
             const float inv = (l_tot == 0.f || l_tot != l_tot) ? 1.f : 1.f / l_tot;   // prefill.cuh:604-605
+            if (p.lse != nullptr && row_ok && wg == 0)
+                p.lse[(int64_t)b * p.lse_batch_stride + (int64_t)h * p.lse_head_stride + q_off + qrow] =
+                    (l_tot == 0.f || l_tot != l_tot) ? -INFINITY : (m_ref * c2 + log2f(l_tot)) * 0.6931471805599453f;
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 uint32_t o[32];

@@ -569,6 +569,9 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     tc_fence_after();
                 }
                 const float inv = (l_run == 0.f || l_run != l_run) ? 1.f : 1.f / l_run;   // prefill.cuh:604-605
+                if (p.lse != nullptr && row_ok)   // natural-log LSE of the scaled scores (the reference drops it, api.cpp:436)
+                    p.lse[(int64_t)w.b * p.lse_batch_stride + (int64_t)w.h * p.lse_head_stride + w.q_off + qrow] =
+                        (l_run == 0.f || l_run != l_run) ? -INFINITY : (m_run * c2 + log2f(l_run)) * 0.6931471805599453f;
 #pragma unroll
                 for (int c = 0; c < DPAD / 32; ++c) {
                     uint32_t o[32];

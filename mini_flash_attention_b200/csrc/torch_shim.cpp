@@ -9,7 +9,9 @@
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
 
+#include <limits>
 #include <optional>
+#include <tuple>
 
 #include "../../include/mfa_b200.h"
 
@@ -56,10 +58,11 @@ void* stream_of(const at::Tensor& t) { return at::cuda::getCurrentCUDAStream(t.g
 
 }  // namespace
 
-// q (B,Sq,H,D); k, v (B,Sk,Hkv,D); returns (B,Sq,H,D).  api.cpp:113-186
-at::Tensor mini_flash_attention_forward(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v,
-                                        std::optional<at::Tensor> out_, bool is_causal, int64_t window_left,
-                                        int64_t window_right) {
+// q (B,Sq,H,D); k, v (B,Sk,Hkv,D); returns (B,Sq,H,D) and, when asked, the natural-log LSE (B,H,Sq) fp32 that the
+// reference computes and drops (api.cpp:436-437).  api.cpp:113-186
+static std::tuple<at::Tensor, at::Tensor> forward_impl(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v,
+                                                       const std::optional<at::Tensor>& out_, bool is_causal,
+                                                       int64_t window_left, int64_t window_right, bool want_lse) {
     check_qkv(q, k, v);
     TORCH_CHECK(q.dim() == 4 && k.dim() == 4 && v.dim() == 4, "q, k, v must be 4-D (batch, seqlen, heads, head_dim)");
     const int64_t batch = q.size(0), seqlen_q = q.size(1), heads = q.size(2), head_dim = q.size(3);
@@ -80,8 +83,13 @@ at::Tensor mini_flash_attention_forward(const at::Tensor& q, const at::Tensor& k
     } else {
         out = at::empty_like(q);
     }
-    if (batch == 0 || seqlen_q == 0 || heads == 0) return out;
-    if (seqlen_k == 0) return out.zero_();
+    at::Tensor lse;
+    if (want_lse) lse = at::empty({batch, heads, seqlen_q}, q.options().dtype(at::kFloat));
+    if (batch == 0 || seqlen_q == 0 || heads == 0) return {out, lse};
+    if (seqlen_k == 0) {
+        if (want_lse) lse.fill_(-std::numeric_limits<float>::infinity());
+        return {out.zero_(), lse};
+    }
     const at::Tensor qc = tma_ready(q), kc = tma_ready(k), vc = tma_ready(v);
     at::Tensor oc = tma_ok(out) ? out : at::empty(out.sizes(), out.options());
 
@@ -96,18 +104,32 @@ at::Tensor mini_flash_attention_forward(const at::Tensor& q, const at::Tensor& k
     P.heads = (int32_t)heads; P.kv_heads = (int32_t)kv_heads; P.batch = (int32_t)batch;
     P.seqlen_q = (int32_t)seqlen_q; P.seqlen_k = (int32_t)seqlen_k; P.head_dim = (int32_t)head_dim;
     P.is_bf16 = q.scalar_type() == at::kBFloat16;
+    if (want_lse) P.softmax_lse_ptr = lse.data_ptr<float>();
     check_rc(mfa_prefill_fwd(&P, stream_of(q)), "mfa_prefill_fwd");
     if (!oc.is_same(out)) out.copy_(oc);
-    return out;
+    return {out, lse};
+}
+
+at::Tensor mini_flash_attention_forward(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v,
+                                        std::optional<at::Tensor> out_, bool is_causal, int64_t window_left,
+                                        int64_t window_right) {
+    return std::get<0>(forward_impl(q, k, v, out_, is_causal, window_left, window_right, false));
+}
+std::tuple<at::Tensor, at::Tensor> mini_flash_attention_forward_lse(const at::Tensor& q, const at::Tensor& k,
+                                                                    const at::Tensor& v, std::optional<at::Tensor> out_,
+                                                                    bool is_causal, int64_t window_left,
+                                                                    int64_t window_right) {
+    return forward_impl(q, k, v, out_, is_causal, window_left, window_right, true);
 }
 
 // Packed variable-length prefill, optionally with paged K/V.  api.cpp:189-267.
 // q (total_q,H,D); k, v (total_k,Hkv,D) or, with block_table (batch,max_blocks) int32, (num_blocks,page,Hkv,D).
-at::Tensor mini_flash_attention_varlen_forward(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v,
-                                               const at::Tensor& cu_seqlens_q, const at::Tensor& cu_seqlens_k,
-                                               int64_t max_seqlen_q, int64_t max_seqlen_k, bool causal,
-                                               int64_t window_left, int64_t window_right,
-                                               std::optional<at::Tensor> block_table) {
+// With want_lse also the LSE, (H, total_q) fp32 (flash-attn's packed layout).
+static std::tuple<at::Tensor, at::Tensor> varlen_impl(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v,
+                                                      const at::Tensor& cu_seqlens_q, const at::Tensor& cu_seqlens_k,
+                                                      int64_t max_seqlen_q, int64_t max_seqlen_k, bool causal,
+                                                      int64_t window_left, int64_t window_right,
+                                                      const std::optional<at::Tensor>& block_table, bool want_lse) {
     check_qkv(q, k, v);
     TORCH_CHECK(cu_seqlens_q.is_cuda(), "cu_seqlens_q must be on CUDA");
     TORCH_CHECK(cu_seqlens_k.is_cuda(), "cu_seqlens_k must be on CUDA");
@@ -121,7 +143,9 @@ at::Tensor mini_flash_attention_varlen_forward(const at::Tensor& q, const at::Te
     check_head_dim(head_dim, heads, kv_heads);
     c10::cuda::CUDAGuard guard(q.device());
     at::Tensor out = at::empty_like(q);
-    if (batch == 0 || total_q == 0 || heads == 0) return out;
+    at::Tensor lse;
+    if (want_lse) lse = at::empty({heads, total_q}, q.options().dtype(at::kFloat));
+    if (batch == 0 || total_q == 0 || heads == 0) return {out, lse};
     const at::Tensor cu_q = cu_seqlens_q.contiguous(), cu_k = cu_seqlens_k.contiguous();
 
     mfa_params_t P{};
@@ -148,7 +172,10 @@ at::Tensor mini_flash_attention_varlen_forward(const at::Tensor& q, const at::Te
         const int64_t total_k = k.size(0);
         TORCH_CHECK(SHAPE_IS(k, total_k, kv_heads, head_dim), "k must have shape (total_k, kv_num_heads, head_dim)");
         TORCH_CHECK(SHAPE_IS(v, total_k, kv_heads, head_dim), "v must have shape (total_k, kv_num_heads, head_dim)");
-        if (total_k == 0) return out.zero_();
+        if (total_k == 0) {
+            if (want_lse) lse.fill_(-std::numeric_limits<float>::infinity());
+            return {out.zero_(), lse};
+        }
         kc = tma_ready(k); vc = tma_ready(v);
         P.total_k = (int32_t)total_k;
         P.k_row_stride = kc.stride(0); P.k_head_stride = kc.stride(1);
@@ -165,8 +192,29 @@ at::Tensor mini_flash_attention_varlen_forward(const at::Tensor& q, const at::Te
     P.is_bf16 = q.scalar_type() == at::kBFloat16;
     P.cu_seqlens_q = cu_q.data_ptr<int32_t>(); P.cu_seqlens_k = cu_k.data_ptr<int32_t>();
     P.total_q = (int32_t)total_q;
+    if (want_lse) {
+        // rows of q past cu_seqlens_q[batch] belong to no sequence and are not written by the kernel
+        lse.fill_(-std::numeric_limits<float>::infinity());
+        P.softmax_lse_ptr = lse.data_ptr<float>();
+    }
     check_rc(mfa_prefill_fwd(&P, stream_of(q)), "mfa_prefill_fwd");
-    return out;
+    return {out, lse};
+}
+
+at::Tensor mini_flash_attention_varlen_forward(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v,
+                                               const at::Tensor& cu_seqlens_q, const at::Tensor& cu_seqlens_k,
+                                               int64_t max_seqlen_q, int64_t max_seqlen_k, bool causal,
+                                               int64_t window_left, int64_t window_right,
+                                               std::optional<at::Tensor> block_table) {
+    return std::get<0>(varlen_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, window_left,
+                                   window_right, block_table, false));
+}
+std::tuple<at::Tensor, at::Tensor> mini_flash_attention_varlen_forward_lse(
+    const at::Tensor& q, const at::Tensor& k, const at::Tensor& v, const at::Tensor& cu_seqlens_q,
+    const at::Tensor& cu_seqlens_k, int64_t max_seqlen_q, int64_t max_seqlen_k, bool causal, int64_t window_left,
+    int64_t window_right, std::optional<at::Tensor> block_table) {
+    return varlen_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, window_left, window_right,
+                       block_table, true);
 }
 
 namespace {
@@ -248,22 +296,41 @@ void run_decode(mfa_params_t& P, const at::Tensor& q) {
 
 // q_len == 1 decode over a contiguous or paged KV cache.  api.cpp:343-446.  `causal` is accepted and ignored exactly
 // like the reference (api.cpp:349, quirk Q10).
-at::Tensor mini_flash_attention_with_kvcache(const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache,
-                                             std::optional<at::Tensor> cache_seqlens,
-                                             std::optional<at::Tensor> block_table, bool /*causal*/, int64_t num_splits) {
+static std::tuple<at::Tensor, at::Tensor> kvcache_impl(const at::Tensor& q, const at::Tensor& k_cache,
+                                                       const at::Tensor& v_cache,
+                                                       const std::optional<at::Tensor>& cache_seqlens,
+                                                       const std::optional<at::Tensor>& block_table, int64_t num_splits,
+                                                       bool want_lse) {
     DecodeCall c;
     decode_params(c, q, k_cache, v_cache, cache_seqlens, block_table, num_splits);
     c10::cuda::CUDAGuard guard(q.device());
     at::Tensor out = at::empty_like(q);   // api.cpp:405
-    if (q.numel() == 0) return out;
-    if (c.P.seqlen_k == 0) return out.zero_();
+    at::Tensor lse;   // (B, H, 1) fp32, the tensor the reference allocates and drops (api.cpp:436-437)
+    if (want_lse) lse = at::empty({q.size(0), q.size(2), 1}, q.options().dtype(at::kFloat));
+    if (q.numel() == 0) return {out, lse};
+    if (c.P.seqlen_k == 0) {
+        if (want_lse) lse.fill_(-std::numeric_limits<float>::infinity());
+        return {out.zero_(), lse};
+    }
     const bool o_ok = reinterpret_cast<uintptr_t>(out.data_ptr()) % 8 == 0 && out.stride(0) % 4 == 0 && out.stride(2) % 4 == 0;
     at::Tensor oc = o_ok ? out : at::empty(out.sizes(), out.options());
     c.P.o_ptr = oc.data_ptr();
     c.P.o_batch_stride = oc.stride(0); c.P.o_row_stride = oc.stride(1); c.P.o_head_stride = oc.stride(2);
+    if (want_lse) c.P.softmax_lse_ptr = lse.data_ptr<float>();
     run_decode(c.P, q);
     if (!oc.is_same(out)) out.copy_(oc);
-    return out;
+    return {out, lse};
+}
+
+at::Tensor mini_flash_attention_with_kvcache(const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache,
+                                             std::optional<at::Tensor> cache_seqlens,
+                                             std::optional<at::Tensor> block_table, bool /*causal*/, int64_t num_splits) {
+    return std::get<0>(kvcache_impl(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, false));
+}
+std::tuple<at::Tensor, at::Tensor> mini_flash_attention_with_kvcache_lse(
+    const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache, std::optional<at::Tensor> cache_seqlens,
+    std::optional<at::Tensor> block_table, bool /*causal*/, int64_t num_splits) {
+    return kvcache_impl(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, true);
 }
 
 // KV-shard building block of the multi-GPU decode: normalised fp32 partial O (B,H,D) and LSE (B,H) over this rank's
@@ -295,6 +362,16 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("block_table") = py::none());
     m.def("mini_flash_attention_with_kvcache", &mini_flash_attention_with_kvcache, py::arg("q"), py::arg("k_cache"),
           py::arg("v_cache"), py::arg("cache_seqlens"), py::arg("block_table"), py::arg("causal"),
+          py::arg("num_splits") = 0);
+    m.def("mini_flash_attention_forward_lse", &mini_flash_attention_forward_lse, py::arg("q"), py::arg("k"), py::arg("v"),
+          py::arg("out") = py::none(), py::arg("is_causal") = false, py::arg("window_size_left") = -1,
+          py::arg("window_size_right") = -1);
+    m.def("mini_flash_attention_varlen_forward_lse", &mini_flash_attention_varlen_forward_lse, py::arg("q"),
+          py::arg("k"), py::arg("v"), py::arg("cu_seqlens_q"), py::arg("cu_seqlens_k"), py::arg("max_seqlen_q"),
+          py::arg("max_seqlen_k"), py::arg("causal"), py::arg("window_size_left"), py::arg("window_size_right"),
+          py::arg("block_table") = py::none());
+    m.def("mini_flash_attention_with_kvcache_lse", &mini_flash_attention_with_kvcache_lse, py::arg("q"),
+          py::arg("k_cache"), py::arg("v_cache"), py::arg("cache_seqlens"), py::arg("block_table"), py::arg("causal"),
           py::arg("num_splits") = 0);
     m.def("decode_partial", &decode_partial, py::arg("q"), py::arg("k_cache"), py::arg("v_cache"),
           py::arg("cache_seqlens"), py::arg("block_table"), py::arg("num_splits") = 0);

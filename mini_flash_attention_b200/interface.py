@@ -18,7 +18,9 @@ def flash_attn_func(
     k: torch.Tensor,
     v: torch.Tensor,
     causal: bool = False,
-) -> torch.Tensor:
+    *,
+    return_lse: bool = False,
+):
     """FlashAttention forward (reference: interface.py:6-37).
 
     Supports MQA/GQA: K, V may have fewer heads than Q (the number of Q heads must be divisible by the number
@@ -30,9 +32,14 @@ def flash_attn_func(
         v: (batch_size, seqlen_k, nheads_k, headdim)
         causal: apply the causal mask.  Like the reference it is aligned to the TOP-LEFT corner
             (key j is visible to query i iff j <= i), which equals the usual convention when seqlen_q == seqlen_k.
+        return_lse: (keyword-only, new -- SURVEY 8f row 1) also return the row-wise log-sum-exp of the scaled scores,
+            which the reference computes and drops; makes the op composable (chunked / ring prefill merges).
     Return:
         out: (batch_size, seqlen_q, nheads, headdim)
+        softmax_lse [if return_lse]: (batch_size, nheads, seqlen_q) fp32, natural log; -inf for rows that see no key
     """
+    if return_lse:
+        return _C.mini_flash_attention_forward_lse(q, k, v, None, causal, -1, -1)
     return _C.mini_flash_attention_forward(q, k, v, None, causal, -1, -1)
 
 
@@ -46,7 +53,9 @@ def flash_attn_varlen_func(
     max_seqlen_k: int,
     causal: bool = False,
     block_table=None,
-) -> torch.Tensor:
+    *,
+    return_lse: bool = False,
+):
     """FlashAttention forward for packed variable-length batches (reference: interface.py:40-92).
 
     Arguments:
@@ -58,12 +67,13 @@ def flash_attn_varlen_func(
         causal: top-left aligned causal mask (see flash_attn_func)
         block_table: optional (batch_size, max_blocks_per_seq) int32 page table; pages are gathered per page
             (any page size that is a multiple of 8), not per 64-row tile.
+        return_lse: (keyword-only, new) also return the log-sum-exp, see flash_attn_func
     Return:
         out: (total_q, nheads, headdim)
+        softmax_lse [if return_lse]: (nheads, total_q) fp32
     """
-    return _C.mini_flash_attention_varlen_forward(
-        q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, -1, -1, block_table
-    )
+    fn = _C.mini_flash_attention_varlen_forward_lse if return_lse else _C.mini_flash_attention_varlen_forward
+    return fn(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, -1, -1, block_table)
 
 
 def flash_attn_with_kvcache(
@@ -75,7 +85,8 @@ def flash_attn_with_kvcache(
     num_splits=0,
     *,
     causal: bool = False,
-) -> torch.Tensor:
+    return_lse: bool = False,
+):
     """Single-token decode against a KV cache (reference: interface.py:95-124).
 
     Arguments:
@@ -86,6 +97,10 @@ def flash_attn_with_kvcache(
         block_table: optional (batch_size, max_blocks_per_seq) int32
         num_splits: KV splits (flash decoding); <= 0 picks automatically
         causal: accepted for compatibility with the reference's tests and ignored (q_len == 1)
+        return_lse: (new) also return softmax_lse (batch_size, nheads, 1) fp32 -- the tensor the reference allocates
+            and drops (api.cpp:436-437)
     """
     assert q.size(1) == 1, "flash_attn_with_kvcache currently only supports seqlen_q=1 for decoding"
+    if return_lse:
+        return _C.mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)
     return _C.mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)

@@ -54,6 +54,21 @@ def attention_ref(q, k, v, causal: bool = False, key_len: Optional[int] = None) 
     return o.permute(0, 2, 1, 3).contiguous()
 
 
+def lse_ref(q, k, causal: bool = False) -> torch.Tensor:
+    """Row-wise natural-log LSE of the scaled, masked scores: q (B,Sq,H,D), k (B,Sk,Hkv,D) -> (B,H,Sq) float32;
+    -inf where a row sees no key.  (The quantity the reference stores in softmax_lse, decode.cuh:750-754.)"""
+    B, Sq, H, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    qf = q.float().permute(0, 2, 1, 3)
+    kf = _expand_kv(k.float(), H // Hkv, 2).permute(0, 2, 1, 3)
+    s = torch.matmul(qf, kf.transpose(-1, -2)) * (1.0 / math.sqrt(D))
+    if causal:
+        row = torch.arange(Sq, device=q.device)[:, None]
+        col = torch.arange(Sk, device=q.device)[None, :]
+        s = s.masked_fill(col > row, float("-inf"))
+    return torch.logsumexp(s, dim=-1)
+
+
 def gather_paged(cache: torch.Tensor, block_table_row: torch.Tensor, length: int) -> torch.Tensor:
     """cache (num_blocks, page, Hkv, D) -> the first `length` logical rows (length, Hkv, D), gathered per row."""
     page = cache.shape[1]

@@ -55,15 +55,23 @@ int main(void) {
 
 def test_python_surface_matches_reference():
     """Signatures verbatim from /root/reference/mini_flash_attention/interface.py:6-11,40-50,95-102
-    (+ the compatible kw-only `causal` on kvcache, SURVEY section 4 observation 1)."""
+    (+ the compatible kw-only `causal` on kvcache, SURVEY section 4 observation 1, and the kw-only, default-off
+    `return_lse` of SURVEY 8f row 1): positional parameters are exactly the reference's."""
+    def positional(f):
+        return [n for n, p in inspect.signature(f).parameters.items() if p.kind is not inspect.Parameter.KEYWORD_ONLY]
+
+    def kw_only(f):
+        return {n: p.default for n, p in inspect.signature(f).parameters.items() if p.kind is inspect.Parameter.KEYWORD_ONLY}
     import mini_flash_attention as m
     assert m.__all__ == ["flash_attn_func", "flash_attn_varlen_func", "flash_attn_with_kvcache"]
-    assert list(inspect.signature(m.flash_attn_func).parameters) == ["q", "k", "v", "causal"]
-    assert list(inspect.signature(m.flash_attn_varlen_func).parameters) == [
+    assert positional(m.flash_attn_func) == ["q", "k", "v", "causal"]
+    assert kw_only(m.flash_attn_func) == {"return_lse": False}
+    assert positional(m.flash_attn_varlen_func) == [
         "q", "k", "v", "cu_seqlens_q", "cu_seqlens_k", "max_seqlen_q", "max_seqlen_k", "causal", "block_table"]
+    assert kw_only(m.flash_attn_varlen_func) == {"return_lse": False}
     sig = inspect.signature(m.flash_attn_with_kvcache)
-    assert list(sig.parameters) == ["q", "k_cache", "v_cache", "cache_seqlens", "block_table", "num_splits", "causal"]
-    assert sig.parameters["causal"].kind is inspect.Parameter.KEYWORD_ONLY
+    assert positional(m.flash_attn_with_kvcache) == ["q", "k_cache", "v_cache", "cache_seqlens", "block_table", "num_splits"]
+    assert kw_only(m.flash_attn_with_kvcache) == {"causal": False, "return_lse": False}
     assert sig.parameters["num_splits"].default == 0
     for name in ("mini_flash_attention_forward", "mini_flash_attention_varlen_forward", "mini_flash_attention_with_kvcache"):
         assert hasattr(m._C, name)
