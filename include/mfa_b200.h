@@ -146,7 +146,7 @@ int mfa_selftest_umma(int mode, const void* a, const void* b, float* d, int kdim
 /* CTA-pair (cluster of 2, tcgen05 cta_group::2) self test / MMA-rate probe (csrc/selftest2_sm100.cu):
  *   mode 0: d[256 x 128] = a[256 x 128] * b[128 x 128]^T  (pair, SS)   mode 1: d = a[256 x 128] * b[128 x 128] (pair, TS)
  *   mode 2 / 3: the same per-CTA tile with a single CTA (rows 0-127 only), for rate comparison.
- *   reps >= 1 repeats the 8 K-steps accumulating; cycles (optional, device int64[1]) receives clock64() ticks. */
+ *   reps >= 1 repeats the 8 K-steps accumulating; cycles (optional, device int64[2]) receives clock64() ticks: [0] until completion, [1] until all MMAs were issued. */
 int mfa_selftest_umma2(int mode, const void* a, const void* b, float* d, int is_bf16, int reps, long long* cycles,
                        void* cuda_stream);
 

@@ -373,6 +373,17 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 __syncwarp();
             };
 
+            // MEASURED LIMITS OF THIS WARP (scripts/umma_rate.py and register-held clock() stamps):
+            //  * tcgen05.mma issue BLOCKS once ~4 SS / ~2 TS instructions are queued, so this thread is never more
+            //    than ~270 / ~150 cycles ahead of the tensor pipe, and whatever it executes between two batches of
+            //    MMAs beyond that slack drains the pipe;
+            //  * an mbarrier try_wait costs ~90 cycles even when the phase completed long ago; with the fence, the
+            //    elect and the descriptor moves each of the 7 waits of a KV step shows up as a 150-250 cycle gap
+            //    (register stamps: MMA issue 2470 cycles + gaps ~1000 = the 3470-cycle KV step).
+            // Tried and measured NOT to help (each within +-5 % of this form): one issuing warp per Q tile with and
+            // without an issue token, P.V + S as one 16-MMA batch (one wait per tile), early non-blocking probes
+            // (test_wait: ptxas consumes the predicate at once, the latency stays exposed), splitting the softmax of
+            // a tile by key columns over both warpgroups.
             int it = 0;                   // K/V ring position, runs across items
             uint32_t q_cnt = 0;           // valid items so far
             uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)

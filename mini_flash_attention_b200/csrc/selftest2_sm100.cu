@@ -19,7 +19,7 @@ namespace {
 struct SelfTest2Params {
     const uint16_t* p;   // mode 1/3: P row-major [256][128] 16-bit
     float* d;            // output row-major [256][128]
-    long long* cycles;   // optional: [0] = cycles for reps*8 MMAs
+    long long* cycles;   // optional: [0] = cycles for reps*8 MMAs to complete, [1] = cycles until all were issued
     int mode, is_bf16, reps;
 };
 
@@ -140,13 +140,17 @@ __global__ void __launch_bounds__(128) umma_selftest2_kernel(const __grid_consta
             }
             __syncwarp();
         }
+        const long long t_issued = clock64();   // all MMAs accepted by the tensor pipe's queue
         if (elect_one()) {
             if (kPair) umma_commit_pair(bar_mma); else umma_commit(bar_mma);
         }
         __syncwarp();
         mbar_wait(bar_mma, 0);
         const long long t1 = clock64();
-        if (p.cycles && lane == 0) p.cycles[0] = t1 - t0;
+        if (p.cycles && lane == 0) {
+            p.cycles[0] = t1 - t0;
+            p.cycles[1] = t_issued - t0;   // issue-side time: shows how far the issuing thread can run ahead
+        }
     }
     mbar_wait(bar_mma, 0);
     tc_fence_after();

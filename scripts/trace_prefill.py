@@ -27,7 +27,7 @@ print("mma events (single): 0 K/V ready, 1 p_lo0 seen, 2 p_hi0 seen, 3 PV0+S0 is
 print("mma events (pair): 0 K(j+1) ready, 4 S(j+1) issued, 5 V(j) ready, 1 p_lo seen, 2 p_hi seen (PV lo issued), 3 PV hi issued")
 n = min(S // 128, 64)
 for j in list(range(0, 6)) + list(range(n - 3, n)):
-    print(f"j={j:2d} WG0 {[r(x) for x in t[0, j, :6]]}  WG1 {[r(x) for x in t[1, j, :6]]}  MMA {[r(x) for x in t[2, j, :7]]}")
+    print(f"j={j:2d} WG0 {[r(x) for x in t[0, j, :6]]}  WG1 {[r(x) for x in t[1, j, :6]]}  MMA {[r(x) for x in t[2, j, :8]]}  top/Vready {[r(x) for x in pr[j, :2]]}")
 import statistics
 for role, ev in ((0, 1), (1, 1), (2, 0)):
     d = [int(t[role, j + 1, ev] - t[role, j, ev]) for j in range(4, n - 2)]

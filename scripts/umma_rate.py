@@ -11,9 +11,9 @@ for mode in (2, 3, 5, 0, 1, 4):
     a = (torch.randn(256, 128, device="cuda") * 0.01).to(torch.bfloat16)
     b = (torch.randn(128, 128, device="cuda") * 0.01).to(torch.bfloat16)
     d = torch.zeros(256, 128, device="cuda")
-    cyc = torch.zeros(1, dtype=torch.int64, device="cuda")
-    for reps in (1, 64, 256):
+    cyc = torch.zeros(2, dtype=torch.int64, device="cuda")
+    for reps in (1, 2, 4, 8, 64, 256):
         rc = lib.mfa_selftest_umma2(mode, a.data_ptr(), b.data_ptr(), d.data_ptr(), 1, reps, cyc.data_ptr(), None)
         torch.cuda.synchronize()
         assert rc == 0
-        print(f"{names[mode]:13s} reps={reps:4d} cycles={int(cyc.item()):8d} per-MMA={int(cyc.item()) / (reps * 8):7.1f}")
+        print(f"{names[mode]:13s} reps={reps:4d} cycles={int(cyc[0]):8d} per-MMA={int(cyc[0]) / (reps * 8):7.1f}   issued after {int(cyc[1]):8d} cycles")
