@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define MFA_B200_ABI_VERSION 1
+#define MFA_B200_ABI_VERSION 2
 
 /* error codes (0 == success).  mfa_last_error() returns the message of the last failure on the
  * calling thread. */
@@ -91,7 +91,10 @@ typedef struct mfa_params {
      * partial O (batch, heads, head_dim) to o_ptr instead of fp16/bf16, and softmax_lse_ptr
      * (required) receives the partial LSE (-inf for empty shards).  New; no reference analogue. */
     int32_t partial_out;
-    int32_t reserved0;
+    /* Prefill only, with is_causal: align the causal mask to the BOTTOM-RIGHT corner -- key col visible iff
+     * col <= row + (len_k - len_q), per sequence (flash-attn >= 2.1 convention; what chunked prefill against a longer
+     * cache needs).  0 = the reference's top-left mask (prefill.cuh:416).  New. */
+    int32_t causal_bottom_right;
 } mfa_params_t;
 
 /* --- introspection ------------------------------------------------------------------------ */
@@ -115,6 +118,33 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream);
 int    mfa_decode_num_splits(const mfa_params_t* p);
 size_t mfa_decode_workspace_bytes(const mfa_params_t* p, int num_splits);
 int    mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_bytes, void* cuda_stream);
+
+/* --- KV-cache append (the reference's docstring mentions it, interface.py:110-111, but does not
+ *     implement it): write s_new new K/V rows per sequence into the cache IN PLACE at logical positions
+ *     seqlens_k[b] .. seqlens_k[b] + s_new - 1 (paged through block_table, or contiguous), and -- when
+ *     seqlens_out != NULL -- store seqlens_k[b] + s_new there, which is the length the following decode call attends
+ *     to (cache_seqlens itself is not modified, like flash-attn's flash_attn_with_kvcache(k=, v=)).  Rows that would
+ *     fall beyond the cache capacity are not written and seqlens_out is clamped to the capacity. */
+typedef struct mfa_append_params {
+    const void* k_new;          /* (batch, s_new, kv_heads, head_dim) fp16/bf16 */
+    const void* v_new;
+    int64_t knew_batch_stride, knew_row_stride, knew_head_stride;   /* elements; last dim contiguous */
+    int64_t vnew_batch_stride, vnew_row_stride, vnew_head_stride;
+    void* k_cache;              /* (batch, seqlen_k, kv_heads, head_dim) or paged (num_blocks, page, kv_heads, head_dim) */
+    void* v_cache;
+    int64_t k_batch_stride, k_row_stride, k_head_stride;   /* batch stride = block stride when paged */
+    int64_t v_batch_stride, v_row_stride, v_head_stride;
+    const int32_t* seqlens_k;   /* (batch) int32 device, required */
+    int32_t* seqlens_out;       /* (batch) int32 device, optional */
+    const int32_t* block_table; /* NULL => contiguous cache */
+    int32_t block_table_batch_stride;
+    int32_t max_blocks_per_seq;
+    int32_t page_block_size;
+    int32_t seqlen_k;           /* capacity in rows of a contiguous cache (paged: max_blocks_per_seq * page) */
+    int32_t batch, s_new, kv_heads, head_dim;   /* head_dim multiple of 8; all 16-byte aligned rows */
+    int32_t is_bf16;            /* element size only (2 bytes either way) */
+} mfa_append_params_t;
+int mfa_kvcache_append(const mfa_append_params_t* p, void* cuda_stream);
 
 /* --- LSE merge of R normalised partial results (the consumer of the multi-GPU all-gather and
  *     the same arithmetic as the reference's combine kernel, decode.cuh:665-755, but with a

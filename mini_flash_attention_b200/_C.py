@@ -70,7 +70,8 @@ def _i32_ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
-def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, window_size_right, _want_lse=False):
+def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, window_size_right, _want_lse=False,
+                                 _bottom_right=False):
     """Fixed-length prefill.  q (B,Sq,H,D); k, v (B,Sk,Hkv,D); returns (B,Sq,H,D).  api.cpp:113-186.
     With _want_lse (the `_lse` entry point) also the natural-log LSE (B,H,Sq) fp32."""
     _check_qkv(q, k, v)
@@ -104,6 +105,7 @@ def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, wind
     P.v_batch_stride, P.v_row_stride, P.v_head_stride = vc.stride(0), vc.stride(1), vc.stride(2)
     P.o_batch_stride, P.o_row_stride, P.o_head_stride = oc.stride(0), oc.stride(1), oc.stride(2)
     P.is_causal = int(bool(is_causal))  # api.cpp:157, :88
+    P.causal_bottom_right = int(bool(_bottom_right))  # new; 0 = the reference's top-left mask
     P.window_size_left, P.window_size_right = int(window_size_left), int(window_size_right)
     P.heads, P.kv_heads, P.batch = num_heads, kv_num_heads, batch
     P.seqlen_q, P.seqlen_k, P.head_dim = seqlen_q, seqlen_k, head_dim
@@ -118,7 +120,8 @@ def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, wind
 
 
 def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal,
-                                        window_size_left, window_size_right, block_table, _want_lse=False):
+                                        window_size_left, window_size_right, block_table, _want_lse=False,
+                                        _bottom_right=False):
     """Packed variable-length prefill, optionally with paged K/V.  api.cpp:189-267.
 
     q (total_q,H,D); k, v (total_k,Hkv,D) or, with block_table (batch,max_blocks) int32,
@@ -174,6 +177,7 @@ def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max
     P.q_row_stride, P.q_head_stride = qc.stride(0), qc.stride(1)
     P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1)
     P.is_causal = int(bool(causal))  # api.cpp:231
+    P.causal_bottom_right = int(bool(_bottom_right))
     P.window_size_left, P.window_size_right = int(window_size_left), int(window_size_right)
     P.heads, P.kv_heads, P.batch = num_heads, kv_num_heads, batch
     P.seqlen_q, P.seqlen_k, P.head_dim = int(max_seqlen_q), int(max_seqlen_k), head_dim
@@ -245,10 +249,12 @@ def _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits):
 
 
 def mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens: Optional[Union[int, torch.Tensor]],
-                                      block_table, causal, num_splits=0, _want_lse=False):
+                                      block_table, causal, num_splits=0, _want_lse=False, _k_new=None, _v_new=None):
     """q_len == 1 decode over a contiguous or paged KV cache.  api.cpp:343-446.
     `causal` is accepted and ignored exactly like the reference (api.cpp:349, quirk Q10)."""
     P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
+    if _k_new is not None or _v_new is not None:
+        keep.append(_append_kv(P, keep, q, k_cache, v_cache, cache_seqlens, _k_new, _v_new))
     out = torch.empty_like(q)  # api.cpp:405
     # (B, H, 1) fp32: the tensor the reference allocates and drops (api.cpp:436-437)
     lse = torch.empty(q.shape[0], q.shape[2], 1, dtype=torch.float32, device=q.device) if _want_lse else None
@@ -274,6 +280,38 @@ def mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens: Option
     if oc is not out:
         out.copy_(oc)
     return (out, lse) if _want_lse else out
+
+
+def _append_kv(P, keep, q, k_cache, v_cache, cache_seqlens, k_new, v_new):
+    """KV-cache append: write the new rows in place at cache_seqlens and point the decode
+    parameter block at cache_seqlens + s_new (a fresh tensor; cache_seqlens itself is not modified)."""
+    _check(k_new is not None and v_new is not None, "k and v must be given together")
+    _check(cache_seqlens is not None, "appending k/v needs cache_seqlens (where to write)")
+    kc, vc = keep[-2], keep[-1]
+    _check(kc is k_cache and vc is v_cache, "appending k/v needs a cache that can be written in place (16-byte aligned, strides multiples of 8)")
+    _check(k_new.is_cuda and v_new.is_cuda, "k and v must be on CUDA")
+    _check(k_new.dtype == q.dtype and v_new.dtype == q.dtype, "k and v must have q's dtype")
+    _check(k_new.dim() == 4 and k_new.shape[0] == q.shape[0] and k_new.shape[2] == P.kv_heads and k_new.shape[3] == P.head_dim,
+           "k must have shape (batch, seqlen_new, kv_num_heads, head_dim)")
+    _check(v_new.shape == k_new.shape, "v must have the same shape as k")
+    kn = _tma_ready(k_new if k_new.stride(-1) == 1 else k_new.contiguous())
+    vn = _tma_ready(v_new if v_new.stride(-1) == 1 else v_new.contiguous())
+    seqlens_new = torch.empty(q.shape[0], dtype=torch.int32, device=q.device)
+    A = _lib.MfaAppendParams()
+    A.k_new, A.v_new = kn.data_ptr(), vn.data_ptr()
+    A.knew_batch_stride, A.knew_row_stride, A.knew_head_stride = kn.stride(0), kn.stride(1), kn.stride(2)
+    A.vnew_batch_stride, A.vnew_row_stride, A.vnew_head_stride = vn.stride(0), vn.stride(1), vn.stride(2)
+    A.k_cache, A.v_cache = kc.data_ptr(), vc.data_ptr()
+    A.k_batch_stride, A.k_row_stride, A.k_head_stride = kc.stride(0), kc.stride(1), kc.stride(2)
+    A.v_batch_stride, A.v_row_stride, A.v_head_stride = vc.stride(0), vc.stride(1), vc.stride(2)
+    A.seqlens_k, A.seqlens_out = P.seqlens_k, seqlens_new.data_ptr()
+    A.block_table, A.block_table_batch_stride = P.block_table, P.block_table_batch_stride
+    A.max_blocks_per_seq, A.page_block_size, A.seqlen_k = P.max_blocks_per_seq, P.page_block_size, P.seqlen_k
+    A.batch, A.s_new, A.kv_heads, A.head_dim, A.is_bf16 = P.batch, k_new.shape[1], P.kv_heads, P.head_dim, P.is_bf16
+    with torch.cuda.device(q.device):
+        _lib.check(_lib.load().mfa_kvcache_append(ctypes.byref(A), _stream_ptr(q.device)), "mfa_kvcache_append")
+    P.seqlens_k = seqlens_new.data_ptr()
+    return (seqlens_new, kn, vn)
 
 
 def decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits=0):
@@ -344,6 +382,29 @@ def mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, bl
     return _py_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits, _want_lse=True)
 
 
+# superset entry points: optional LSE; causal mask aligned bottom-right; in-place k/v append before the decode
+def mini_flash_attention_forward_ext(q, k, v, out, is_causal, window_size_left, window_size_right, return_lse, bottom_right):
+    r = _py_forward(q, k, v, out, is_causal, window_size_left, window_size_right, _want_lse=return_lse, _bottom_right=bottom_right)
+    return r if return_lse else (r, None)
+
+
+def mini_flash_attention_varlen_forward_ext(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal,
+                                            window_size_left, window_size_right, block_table, return_lse, bottom_right):
+    r = _py_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, window_size_left,
+                           window_size_right, block_table, _want_lse=return_lse, _bottom_right=bottom_right)
+    return r if return_lse else (r, None)
+
+
+def mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits, return_lse,
+                                          k_new, v_new):
+    r = _py_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits, _want_lse=return_lse,
+                         _k_new=k_new, _v_new=v_new)
+    return r if return_lse else (r, None)
+
+
+_py_forward_ext = mini_flash_attention_forward_ext
+_py_varlen_forward_ext = mini_flash_attention_varlen_forward_ext
+_py_with_kvcache_ext = mini_flash_attention_with_kvcache_ext
 _py_forward_lse = mini_flash_attention_forward_lse
 _py_varlen_forward_lse = mini_flash_attention_varlen_forward_lse
 _py_with_kvcache_lse = mini_flash_attention_with_kvcache_lse
@@ -362,7 +423,7 @@ def _load_compiled_shim():
         if _os.environ.get("MFA_B200_SHIM", "").lower() in ("cpp", "compiled"):
             raise
         return None
-    if not hasattr(m, "mini_flash_attention_with_kvcache_lse"):   # built from an older torch_shim.cpp: rebuild with build()
+    if not hasattr(m, "mini_flash_attention_with_kvcache_ext"):   # built from an older torch_shim.cpp: rebuild with build()
         _shim_error = ImportError("stale _mfa_torch_shim module (run python -m mini_flash_attention_b200.build)")
         return None
     return m
@@ -391,6 +452,16 @@ if _shim is not None:
         if isinstance(cache_seqlens, int):
             cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
         return _shim.mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)
+
+    mini_flash_attention_forward_ext = _shim.mini_flash_attention_forward_ext
+    mini_flash_attention_varlen_forward_ext = _shim.mini_flash_attention_varlen_forward_ext
+
+    def mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits,
+                                              return_lse, k_new, v_new):
+        if isinstance(cache_seqlens, int):
+            cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
+        return _shim.mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal,
+                                                           num_splits, return_lse, k_new, v_new)
 
     mini_flash_attention_with_kvcache.__doc__ = _py_with_kvcache.__doc__
     decode_partial.__doc__ = _py_decode_partial.__doc__

@@ -13,7 +13,7 @@ _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MFA_B200_LIB") or os.path.join(_PKG_DIR, "libmfa_b200.so")
 
 MFA_OK = 0
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class MfaParams(ctypes.Structure):
@@ -39,7 +39,24 @@ class MfaParams(ctypes.Structure):
         ("seqlens_k", ctypes.c_void_p),
         ("num_splits", ctypes.c_int32),
         ("softmax_lse_ptr", ctypes.c_void_p),
-        ("partial_out", ctypes.c_int32), ("reserved0", ctypes.c_int32),
+        ("partial_out", ctypes.c_int32), ("causal_bottom_right", ctypes.c_int32),
+    ]
+
+
+class MfaAppendParams(ctypes.Structure):
+    """Mirror of mfa_append_params_t (include/mfa_b200.h)."""
+    _fields_ = [
+        ("k_new", ctypes.c_void_p), ("v_new", ctypes.c_void_p),
+        ("knew_batch_stride", ctypes.c_int64), ("knew_row_stride", ctypes.c_int64), ("knew_head_stride", ctypes.c_int64),
+        ("vnew_batch_stride", ctypes.c_int64), ("vnew_row_stride", ctypes.c_int64), ("vnew_head_stride", ctypes.c_int64),
+        ("k_cache", ctypes.c_void_p), ("v_cache", ctypes.c_void_p),
+        ("k_batch_stride", ctypes.c_int64), ("k_row_stride", ctypes.c_int64), ("k_head_stride", ctypes.c_int64),
+        ("v_batch_stride", ctypes.c_int64), ("v_row_stride", ctypes.c_int64), ("v_head_stride", ctypes.c_int64),
+        ("seqlens_k", ctypes.c_void_p), ("seqlens_out", ctypes.c_void_p), ("block_table", ctypes.c_void_p),
+        ("block_table_batch_stride", ctypes.c_int32), ("max_blocks_per_seq", ctypes.c_int32),
+        ("page_block_size", ctypes.c_int32), ("seqlen_k", ctypes.c_int32),
+        ("batch", ctypes.c_int32), ("s_new", ctypes.c_int32), ("kv_heads", ctypes.c_int32), ("head_dim", ctypes.c_int32),
+        ("is_bf16", ctypes.c_int32),
     ]
 
 
@@ -47,7 +64,7 @@ class MfaParams(ctypes.Structure):
 EXPORTS = (
     "mfa_abi_version", "mfa_last_error", "mfa_device_supported", "mfa_prefill_fwd", "mfa_decode_num_splits",
     "mfa_decode_workspace_bytes", "mfa_decode_fwd", "mfa_combine_partials", "mfa_launch_count", "mfa_selftest_umma",
-    "mfa_debug_set_trace", "mfa_selftest_umma2", "mfa_debug_set_prefill_impl",
+    "mfa_debug_set_trace", "mfa_selftest_umma2", "mfa_debug_set_prefill_impl", "mfa_kvcache_append",
 )
 
 _lib = None
@@ -82,6 +99,8 @@ def load() -> ctypes.CDLL:
                                          ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
     lib.mfa_combine_partials.restype = ctypes.c_int
     lib.mfa_launch_count.restype = ctypes.c_uint64
+    lib.mfa_kvcache_append.argtypes = [ctypes.POINTER(MfaAppendParams), ctypes.c_void_p]
+    lib.mfa_kvcache_append.restype = ctypes.c_int
     lib.mfa_debug_set_trace.argtypes = [ctypes.c_void_p]
     lib.mfa_debug_set_trace.restype = None
     lib.mfa_debug_set_prefill_impl.argtypes = [ctypes.c_int]

@@ -26,6 +26,7 @@ cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const
 int prefill_rows_per_cta(int dpad);
 cudaError_t launch_prefill_pair(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                 const PrefillKParams& p, bool is_bf16, cudaStream_t stream);
+cudaError_t launch_kvcache_append(const mfa_append_params_t& p, int sm_count, cudaStream_t stream);
 }  // namespace mfa
 
 namespace {
@@ -145,7 +146,8 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
 
     // head_dim in (64, 128] has two kernels: the single-CTA one (prefill_sm100.cu, default: faster today) and the
     // CTA-pair one (prefill_pair_sm100.cu; MFA_PREFILL_IMPL=pair or mfa_debug_set_prefill_impl(1) selects it).
-    const bool use_pair = (dpad == 128) && (g_prefill_impl.load() == 1);
+    // (the opt-in pair kernel implements the reference's top-left mask only)
+    const bool use_pair = (dpad == 128) && (g_prefill_impl.load() == 1) && !(p->is_causal && p->causal_bottom_right);
     const int kv_tile_box = use_pair ? 64 : mfa::kPrefillBlockN;
 
     CUtensorMap tmQ, tmK, tmV;
@@ -208,6 +210,7 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     kp.seqlen_q = p->seqlen_q;
     kp.seqlen_k = p->seqlen_k;
     kp.is_causal = p->is_causal ? 1 : 0;
+    kp.causal_br = (p->is_causal && p->causal_bottom_right) ? 1 : 0;
     const int rows_per_cta = mfa::prefill_rows_per_cta(dpad);
     kp.num_m_blocks = (p->seqlen_q + rows_per_cta - 1) / rows_per_cta;
     kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);   // api.cpp:99
@@ -376,6 +379,32 @@ int mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_byte
         if (e != cudaSuccess) return cuda_fail(e, "combine launch");
         g_launches.fetch_add(1);
     }
+    return MFA_OK;
+}
+
+// ------------------------------------------------------------------------------------------ KV-cache append
+int mfa_kvcache_append(const mfa_append_params_t* p, void* cuda_stream) {
+    if (!p) return fail(MFA_ERR_INVALID_ARG, "null params");
+    if (!p->k_new || !p->v_new || !p->k_cache || !p->v_cache) return fail(MFA_ERR_INVALID_ARG, "null tensor pointer");
+    if (!p->seqlens_k) return fail(MFA_ERR_INVALID_ARG, "kv-cache append needs seqlens_k (where to write)");
+    if (p->batch < 0 || p->s_new < 0 || p->kv_heads <= 0) return fail(MFA_ERR_INVALID_ARG, "bad batch / s_new / kv_heads");
+    if (p->head_dim <= 0 || p->head_dim > 256 || p->head_dim % 8) return fail(MFA_ERR_UNSUPPORTED, "head_dim must be a multiple of 8, <= 256");
+    if (p->block_table && (p->page_block_size <= 0 || p->max_blocks_per_seq <= 0))
+        return fail(MFA_ERR_INVALID_ARG, "paged append needs page_block_size and max_blocks_per_seq");
+    auto mult8 = [](int64_t v) { return (v % 8) == 0; };
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (!al16(p->k_new) || !al16(p->v_new) || !al16(p->k_cache) || !al16(p->v_cache) || !mult8(p->knew_batch_stride) ||
+        !mult8(p->knew_row_stride) || !mult8(p->knew_head_stride) || !mult8(p->vnew_batch_stride) ||
+        !mult8(p->vnew_row_stride) || !mult8(p->vnew_head_stride) || !mult8(p->k_batch_stride) ||
+        !mult8(p->k_row_stride) || !mult8(p->k_head_stride) || !mult8(p->v_batch_stride) || !mult8(p->v_row_stride) ||
+        !mult8(p->v_head_stride))
+        return fail(MFA_ERR_INVALID_ARG, "append: pointers must be 16-byte aligned and strides multiples of 8 elements");
+    int rc = check_device();
+    if (rc) return rc;
+    if (p->batch == 0 || p->s_new == 0) return MFA_OK;
+    cudaError_t e = mfa::launch_kvcache_append(*p, sm_count(), static_cast<cudaStream_t>(cuda_stream));
+    if (e != cudaSuccess) return cuda_fail(e, "kvcache append launch");
+    g_launches.fetch_add(1);
     return MFA_OK;
 }
 

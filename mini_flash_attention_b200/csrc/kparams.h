@@ -63,6 +63,7 @@ struct PrefillKParams {
     int32_t heads, kv_heads, group, batch, head_dim;
     int32_t seqlen_q, seqlen_k;    // fixed lengths or max lengths
     int32_t is_causal;
+    int32_t causal_br;             // causal mask aligned to the bottom-right corner: col <= row + (len_k - len_q)
     int32_t num_m_blocks;          // ceil(seqlen_q / 256)
     float scale, scale_log2;
     float* lse;                    // optional natural-log LSE: (B, H, Sq) fixed / (H, total_q) packed; -inf for empty rows

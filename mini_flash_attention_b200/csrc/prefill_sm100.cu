@@ -138,6 +138,7 @@ __device__ __forceinline__ uint64_t exp2_poly2(uint64_t x2) {
 // One work item = (m-block of kNQ*128 query rows, head, sequence).
 struct PrefillItem {
     int h, b, kh, q_off, k_off, len_q, len_k, m0, n_max;
+    int shift;   // causal: key col visible iff col <= row + shift (0 = top-left like the reference, len_k - len_q = bottom-right)
     int n_i[2];
     bool valid;
 };
@@ -161,6 +162,7 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
         w.k_off = p.cu_seqlens_k[w.b];
         w.len_k = p.cu_seqlens_k[w.b + 1] - w.k_off;
     }
+    w.shift = p.causal_br ? (w.len_k - w.len_q) : 0;
     w.m0 = mblk * (kNQ * kPrefillBlockM);
     w.valid = w.m0 < w.len_q;   // prefill.cuh:724-726: tiles past the sequence's own length do nothing
     const int n_tiles_k = (w.len_k + kPrefillBlockN - 1) / kPrefillBlockN;
@@ -168,7 +170,9 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
 #pragma unroll
     for (int i = 0; i < kNQ; ++i) {
         const int r0 = w.m0 + i * kPrefillBlockM;
-        if (r0 < w.len_q) w.n_i[i] = p.is_causal ? min(n_tiles_k, r0 / kPrefillBlockN + 1) : n_tiles_k;
+        // causal: the tile's last row r0+127 sees cols <= r0+127+shift (none at all when that is negative)
+        if (r0 < w.len_q)
+            w.n_i[i] = p.is_causal ? min(n_tiles_k, max(0, (r0 + kPrefillBlockM + w.shift + kPrefillBlockN - 1) / kPrefillBlockN)) : n_tiles_k;
     }
     w.n_max = max(w.n_i[0], w.n_i[1]);
     return w;
@@ -486,9 +490,9 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 MFA_TR(i, j, 2);
 
                 const int col0 = j * kBN;
-                const bool need_mask = (col0 + kBN > len_k) || (p.is_causal && (col0 + kBN - 1 > m0 + i * kBM));
+                const bool need_mask = (col0 + kBN > len_k) || (p.is_causal && (col0 + kBN - 1 > m0 + i * kBM + w.shift));
                 if (need_mask) {
-                    const int lim = p.is_causal ? min(len_k, qrow + 1) : len_k;   // cols >= lim are masked
+                    const int lim = p.is_causal ? min(len_k, qrow + 1 + w.shift) : len_k;   // cols >= lim are masked
 #pragma unroll
                     for (int c = 0; c < 128; ++c)
                         if (col0 + c >= lim) su[c] = 0xff800000u;   // -inf

@@ -62,7 +62,8 @@ void* stream_of(const at::Tensor& t) { return at::cuda::getCurrentCUDAStream(t.g
 // reference computes and drops (api.cpp:436-437).  api.cpp:113-186
 static std::tuple<at::Tensor, at::Tensor> forward_impl(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v,
                                                        const std::optional<at::Tensor>& out_, bool is_causal,
-                                                       int64_t window_left, int64_t window_right, bool want_lse) {
+                                                       int64_t window_left, int64_t window_right, bool want_lse,
+                                                       bool bottom_right = false) {
     check_qkv(q, k, v);
     TORCH_CHECK(q.dim() == 4 && k.dim() == 4 && v.dim() == 4, "q, k, v must be 4-D (batch, seqlen, heads, head_dim)");
     const int64_t batch = q.size(0), seqlen_q = q.size(1), heads = q.size(2), head_dim = q.size(3);
@@ -100,6 +101,7 @@ static std::tuple<at::Tensor, at::Tensor> forward_impl(const at::Tensor& q, cons
     P.v_batch_stride = vc.stride(0); P.v_row_stride = vc.stride(1); P.v_head_stride = vc.stride(2);
     P.o_batch_stride = oc.stride(0); P.o_row_stride = oc.stride(1); P.o_head_stride = oc.stride(2);
     P.is_causal = is_causal ? 1 : 0;   // api.cpp:157, :88
+    P.causal_bottom_right = bottom_right ? 1 : 0;   // new; 0 = the reference's top-left mask
     P.window_size_left = (int32_t)window_left; P.window_size_right = (int32_t)window_right;
     P.heads = (int32_t)heads; P.kv_heads = (int32_t)kv_heads; P.batch = (int32_t)batch;
     P.seqlen_q = (int32_t)seqlen_q; P.seqlen_k = (int32_t)seqlen_k; P.head_dim = (int32_t)head_dim;
@@ -121,6 +123,13 @@ std::tuple<at::Tensor, at::Tensor> mini_flash_attention_forward_lse(const at::Te
                                                                     int64_t window_right) {
     return forward_impl(q, k, v, out_, is_causal, window_left, window_right, true);
 }
+// superset entry point: optional LSE, causal mask aligned bottom-right
+std::tuple<at::Tensor, std::optional<at::Tensor>> mini_flash_attention_forward_ext(
+    const at::Tensor& q, const at::Tensor& k, const at::Tensor& v, std::optional<at::Tensor> out_, bool is_causal,
+    int64_t window_left, int64_t window_right, bool return_lse, bool bottom_right) {
+    auto r = forward_impl(q, k, v, out_, is_causal, window_left, window_right, return_lse, bottom_right);
+    return {std::get<0>(r), return_lse ? std::optional<at::Tensor>(std::get<1>(r)) : std::nullopt};
+}
 
 // Packed variable-length prefill, optionally with paged K/V.  api.cpp:189-267.
 // q (total_q,H,D); k, v (total_k,Hkv,D) or, with block_table (batch,max_blocks) int32, (num_blocks,page,Hkv,D).
@@ -129,7 +138,8 @@ static std::tuple<at::Tensor, at::Tensor> varlen_impl(const at::Tensor& q, const
                                                       const at::Tensor& cu_seqlens_q, const at::Tensor& cu_seqlens_k,
                                                       int64_t max_seqlen_q, int64_t max_seqlen_k, bool causal,
                                                       int64_t window_left, int64_t window_right,
-                                                      const std::optional<at::Tensor>& block_table, bool want_lse) {
+                                                      const std::optional<at::Tensor>& block_table, bool want_lse,
+                                                      bool bottom_right = false) {
     check_qkv(q, k, v);
     TORCH_CHECK(cu_seqlens_q.is_cuda(), "cu_seqlens_q must be on CUDA");
     TORCH_CHECK(cu_seqlens_k.is_cuda(), "cu_seqlens_k must be on CUDA");
@@ -186,6 +196,7 @@ static std::tuple<at::Tensor, at::Tensor> varlen_impl(const at::Tensor& q, const
     P.q_row_stride = qc.stride(0); P.q_head_stride = qc.stride(1);
     P.o_row_stride = out.stride(0); P.o_head_stride = out.stride(1);
     P.is_causal = causal ? 1 : 0;   // api.cpp:231
+    P.causal_bottom_right = bottom_right ? 1 : 0;
     P.window_size_left = (int32_t)window_left; P.window_size_right = (int32_t)window_right;
     P.heads = (int32_t)heads; P.kv_heads = (int32_t)kv_heads; P.batch = (int32_t)batch;
     P.seqlen_q = (int32_t)max_seqlen_q; P.seqlen_k = (int32_t)max_seqlen_k; P.head_dim = (int32_t)head_dim;
@@ -215,6 +226,14 @@ std::tuple<at::Tensor, at::Tensor> mini_flash_attention_varlen_forward_lse(
     int64_t window_right, std::optional<at::Tensor> block_table) {
     return varlen_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, window_left, window_right,
                        block_table, true);
+}
+std::tuple<at::Tensor, std::optional<at::Tensor>> mini_flash_attention_varlen_forward_ext(
+    const at::Tensor& q, const at::Tensor& k, const at::Tensor& v, const at::Tensor& cu_seqlens_q,
+    const at::Tensor& cu_seqlens_k, int64_t max_seqlen_q, int64_t max_seqlen_k, bool causal, int64_t window_left,
+    int64_t window_right, std::optional<at::Tensor> block_table, bool return_lse, bool bottom_right) {
+    auto r = varlen_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, window_left,
+                         window_right, block_table, return_lse, bottom_right);
+    return {std::get<0>(r), return_lse ? std::optional<at::Tensor>(std::get<1>(r)) : std::nullopt};
 }
 
 namespace {
@@ -300,10 +319,44 @@ static std::tuple<at::Tensor, at::Tensor> kvcache_impl(const at::Tensor& q, cons
                                                        const at::Tensor& v_cache,
                                                        const std::optional<at::Tensor>& cache_seqlens,
                                                        const std::optional<at::Tensor>& block_table, int64_t num_splits,
-                                                       bool want_lse) {
+                                                       bool want_lse,
+                                                       const std::optional<at::Tensor>& k_new = std::nullopt,
+                                                       const std::optional<at::Tensor>& v_new = std::nullopt) {
     DecodeCall c;
     decode_params(c, q, k_cache, v_cache, cache_seqlens, block_table, num_splits);
     c10::cuda::CUDAGuard guard(q.device());
+    at::Tensor seqlens_new;
+    if (k_new.has_value() || v_new.has_value()) {
+        // KV-cache append: write the new rows at cache_seqlens, attend to cache_seqlens + s_new
+        TORCH_CHECK(k_new.has_value() && v_new.has_value(), "k and v must be given together");
+        TORCH_CHECK(cache_seqlens.has_value(), "appending k/v needs cache_seqlens (where to write)");
+        TORCH_CHECK(c.k.is_same(k_cache) && c.v.is_same(v_cache), "appending k/v needs a cache that can be written in place (16-byte aligned, strides multiples of 8)");
+        const at::Tensor& kn = *k_new;
+        const at::Tensor& vn = *v_new;
+        TORCH_CHECK(kn.is_cuda() && vn.is_cuda(), "k and v must be on CUDA");
+        TORCH_CHECK(kn.scalar_type() == q.scalar_type() && vn.scalar_type() == q.scalar_type(), "k and v must have q's dtype");
+        TORCH_CHECK(kn.dim() == 4 && kn.size(0) == q.size(0) && kn.size(2) == c.P.kv_heads && kn.size(3) == c.P.head_dim,
+                    "k must have shape (batch, seqlen_new, kv_num_heads, head_dim)");
+        TORCH_CHECK(vn.sizes() == kn.sizes(), "v must have the same shape as k");
+        const at::Tensor knc = tma_ready(kn.stride(-1) == 1 ? kn : kn.contiguous());
+        const at::Tensor vnc = tma_ready(vn.stride(-1) == 1 ? vn : vn.contiguous());
+        seqlens_new = at::empty({q.size(0)}, q.options().dtype(at::kInt));
+        mfa_append_params_t A{};
+        A.k_new = knc.data_ptr(); A.v_new = vnc.data_ptr();
+        A.knew_batch_stride = knc.stride(0); A.knew_row_stride = knc.stride(1); A.knew_head_stride = knc.stride(2);
+        A.vnew_batch_stride = vnc.stride(0); A.vnew_row_stride = vnc.stride(1); A.vnew_head_stride = vnc.stride(2);
+        A.k_cache = c.k.data_ptr(); A.v_cache = c.v.data_ptr();
+        A.k_batch_stride = c.k.stride(0); A.k_row_stride = c.k.stride(1); A.k_head_stride = c.k.stride(2);
+        A.v_batch_stride = c.v.stride(0); A.v_row_stride = c.v.stride(1); A.v_head_stride = c.v.stride(2);
+        A.seqlens_k = c.P.seqlens_k; A.seqlens_out = seqlens_new.data_ptr<int32_t>();
+        A.block_table = c.P.block_table; A.block_table_batch_stride = c.P.block_table_batch_stride;
+        A.max_blocks_per_seq = c.P.max_blocks_per_seq; A.page_block_size = c.P.page_block_size;
+        A.seqlen_k = c.P.seqlen_k;
+        A.batch = c.P.batch; A.s_new = (int32_t)kn.size(1); A.kv_heads = c.P.kv_heads; A.head_dim = c.P.head_dim;
+        A.is_bf16 = c.P.is_bf16;
+        check_rc(mfa_kvcache_append(&A, stream_of(q)), "mfa_kvcache_append");
+        c.P.seqlens_k = seqlens_new.data_ptr<int32_t>();
+    }
     at::Tensor out = at::empty_like(q);   // api.cpp:405
     at::Tensor lse;   // (B, H, 1) fp32, the tensor the reference allocates and drops (api.cpp:436-437)
     if (want_lse) lse = at::empty({q.size(0), q.size(2), 1}, q.options().dtype(at::kFloat));
@@ -331,6 +384,13 @@ std::tuple<at::Tensor, at::Tensor> mini_flash_attention_with_kvcache_lse(
     const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache, std::optional<at::Tensor> cache_seqlens,
     std::optional<at::Tensor> block_table, bool /*causal*/, int64_t num_splits) {
     return kvcache_impl(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, true);
+}
+std::tuple<at::Tensor, std::optional<at::Tensor>> mini_flash_attention_with_kvcache_ext(
+    const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache, std::optional<at::Tensor> cache_seqlens,
+    std::optional<at::Tensor> block_table, bool /*causal*/, int64_t num_splits, bool return_lse,
+    std::optional<at::Tensor> k_new, std::optional<at::Tensor> v_new) {
+    auto r = kvcache_impl(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, return_lse, k_new, v_new);
+    return {std::get<0>(r), return_lse ? std::optional<at::Tensor>(std::get<1>(r)) : std::nullopt};
 }
 
 // KV-shard building block of the multi-GPU decode: normalised fp32 partial O (B,H,D) and LSE (B,H) over this rank's
@@ -373,6 +433,16 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("mini_flash_attention_with_kvcache_lse", &mini_flash_attention_with_kvcache_lse, py::arg("q"),
           py::arg("k_cache"), py::arg("v_cache"), py::arg("cache_seqlens"), py::arg("block_table"), py::arg("causal"),
           py::arg("num_splits") = 0);
+    m.def("mini_flash_attention_forward_ext", &mini_flash_attention_forward_ext, py::arg("q"), py::arg("k"), py::arg("v"),
+          py::arg("out"), py::arg("is_causal"), py::arg("window_size_left"), py::arg("window_size_right"),
+          py::arg("return_lse"), py::arg("bottom_right"));
+    m.def("mini_flash_attention_varlen_forward_ext", &mini_flash_attention_varlen_forward_ext, py::arg("q"),
+          py::arg("k"), py::arg("v"), py::arg("cu_seqlens_q"), py::arg("cu_seqlens_k"), py::arg("max_seqlen_q"),
+          py::arg("max_seqlen_k"), py::arg("causal"), py::arg("window_size_left"), py::arg("window_size_right"),
+          py::arg("block_table"), py::arg("return_lse"), py::arg("bottom_right"));
+    m.def("mini_flash_attention_with_kvcache_ext", &mini_flash_attention_with_kvcache_ext, py::arg("q"),
+          py::arg("k_cache"), py::arg("v_cache"), py::arg("cache_seqlens"), py::arg("block_table"), py::arg("causal"),
+          py::arg("num_splits"), py::arg("return_lse"), py::arg("k_new"), py::arg("v_new"));
     m.def("decode_partial", &decode_partial, py::arg("q"), py::arg("k_cache"), py::arg("v_cache"),
           py::arg("cache_seqlens"), py::arg("block_table"), py::arg("num_splits") = 0);
 }

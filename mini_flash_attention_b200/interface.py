@@ -20,6 +20,7 @@ def flash_attn_func(
     causal: bool = False,
     *,
     return_lse: bool = False,
+    bottom_right: bool = False,
 ):
     """FlashAttention forward (reference: interface.py:6-37).
 
@@ -32,12 +33,18 @@ def flash_attn_func(
         v: (batch_size, seqlen_k, nheads_k, headdim)
         causal: apply the causal mask.  Like the reference it is aligned to the TOP-LEFT corner
             (key j is visible to query i iff j <= i), which equals the usual convention when seqlen_q == seqlen_k.
+        bottom_right: (keyword-only, new -- SURVEY 8f row 2, quirk Q1) with causal=True align the mask to the
+            BOTTOM-RIGHT corner instead: key j visible to query i iff j <= i + (seqlen_k - seqlen_q), the flash-attn
+            >= 2.1 convention and what a chunk of new queries against a longer cache needs.  Default off = reference.
         return_lse: (keyword-only, new -- SURVEY 8f row 1) also return the row-wise log-sum-exp of the scaled scores,
             which the reference computes and drops; makes the op composable (chunked / ring prefill merges).
     Return:
         out: (batch_size, seqlen_q, nheads, headdim)
         softmax_lse [if return_lse]: (batch_size, nheads, seqlen_q) fp32, natural log; -inf for rows that see no key
     """
+    if bottom_right:
+        out, lse = _C.mini_flash_attention_forward_ext(q, k, v, None, causal, -1, -1, return_lse, True)
+        return (out, lse) if return_lse else out
     if return_lse:
         return _C.mini_flash_attention_forward_lse(q, k, v, None, causal, -1, -1)
     return _C.mini_flash_attention_forward(q, k, v, None, causal, -1, -1)
@@ -55,6 +62,7 @@ def flash_attn_varlen_func(
     block_table=None,
     *,
     return_lse: bool = False,
+    bottom_right: bool = False,
 ):
     """FlashAttention forward for packed variable-length batches (reference: interface.py:40-92).
 
@@ -68,10 +76,15 @@ def flash_attn_varlen_func(
         block_table: optional (batch_size, max_blocks_per_seq) int32 page table; pages are gathered per page
             (any page size that is a multiple of 8), not per 64-row tile.
         return_lse: (keyword-only, new) also return the log-sum-exp, see flash_attn_func
+        bottom_right: (keyword-only, new) bottom-right aligned causal mask per sequence, see flash_attn_func
     Return:
         out: (total_q, nheads, headdim)
         softmax_lse [if return_lse]: (nheads, total_q) fp32
     """
+    if bottom_right:
+        out, lse = _C.mini_flash_attention_varlen_forward_ext(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
+                                                              max_seqlen_k, causal, -1, -1, block_table, return_lse, True)
+        return (out, lse) if return_lse else out
     fn = _C.mini_flash_attention_varlen_forward_lse if return_lse else _C.mini_flash_attention_varlen_forward
     return fn(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, -1, -1, block_table)
 
@@ -86,6 +99,8 @@ def flash_attn_with_kvcache(
     *,
     causal: bool = False,
     return_lse: bool = False,
+    k: Optional[torch.Tensor] = None,
+    v: Optional[torch.Tensor] = None,
 ):
     """Single-token decode against a KV cache (reference: interface.py:95-124).
 
@@ -97,10 +112,18 @@ def flash_attn_with_kvcache(
         block_table: optional (batch_size, max_blocks_per_seq) int32
         num_splits: KV splits (flash decoding); <= 0 picks automatically
         causal: accepted for compatibility with the reference's tests and ignored (q_len == 1)
+        k, v: (new -- SURVEY 8f row 2; the semantics the reference's docstring describes at interface.py:110-111 but
+            does not implement) (batch_size, seqlen_new, nheads_k, headdim) new keys/values: written IN PLACE into the
+            cache at positions cache_seqlens[b] .. + seqlen_new - 1 (through block_table when paged) before the
+            attention, which then covers cache_seqlens + seqlen_new keys.  cache_seqlens itself is not modified.
         return_lse: (new) also return softmax_lse (batch_size, nheads, 1) fp32 -- the tensor the reference allocates
             and drops (api.cpp:436-437)
     """
     assert q.size(1) == 1, "flash_attn_with_kvcache currently only supports seqlen_q=1 for decoding"
+    if k is not None or v is not None:
+        out, lse = _C.mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal,
+                                                            num_splits, return_lse, k, v)
+        return (out, lse) if return_lse else out
     if return_lse:
         return _C.mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)
     return _C.mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)

@@ -34,8 +34,9 @@ def _expand_kv(x: torch.Tensor, group: int, dim: int) -> torch.Tensor:
     return x if group == 1 else x.repeat_interleave(group, dim=dim)
 
 
-def attention_ref(q, k, v, causal: bool = False, key_len: Optional[int] = None) -> torch.Tensor:
-    """q (B,Sq,H,D), k/v (B,Sk,Hkv,D) -> (B,Sq,H,D) float32.  Top-left causal (col > row masked)."""
+def attention_ref(q, k, v, causal: bool = False, key_len: Optional[int] = None, bottom_right: bool = False) -> torch.Tensor:
+    """q (B,Sq,H,D), k/v (B,Sk,Hkv,D) -> (B,Sq,H,D) float32.  Top-left causal (col > row masked, the reference's
+    prefill.cuh:416) or, with bottom_right, col > row + (Sk - Sq) masked (flash-attn >= 2.1)."""
     B, Sq, H, D = q.shape
     Sk, Hkv = k.shape[1], k.shape[2]
     qf = q.float().permute(0, 2, 1, 3)
@@ -47,14 +48,14 @@ def attention_ref(q, k, v, causal: bool = False, key_len: Optional[int] = None) 
     if causal:
         row = torch.arange(Sq, device=q.device)[:, None]
         col = torch.arange(Sk, device=q.device)[None, :]
-        s = s.masked_fill(col > row, float("-inf"))
+        s = s.masked_fill(col > row + ((Sk - Sq) if bottom_right else 0), float("-inf"))
     p = torch.softmax(s, dim=-1)
     p = torch.nan_to_num(p, nan=0.0)  # fully masked rows => 0 output (prefill.cuh:604-605)
     o = torch.matmul(p, vf)
     return o.permute(0, 2, 1, 3).contiguous()
 
 
-def lse_ref(q, k, causal: bool = False) -> torch.Tensor:
+def lse_ref(q, k, causal: bool = False, bottom_right: bool = False) -> torch.Tensor:
     """Row-wise natural-log LSE of the scaled, masked scores: q (B,Sq,H,D), k (B,Sk,Hkv,D) -> (B,H,Sq) float32;
     -inf where a row sees no key.  (The quantity the reference stores in softmax_lse, decode.cuh:750-754.)"""
     B, Sq, H, D = q.shape
@@ -65,7 +66,7 @@ def lse_ref(q, k, causal: bool = False) -> torch.Tensor:
     if causal:
         row = torch.arange(Sq, device=q.device)[:, None]
         col = torch.arange(Sk, device=q.device)[None, :]
-        s = s.masked_fill(col > row, float("-inf"))
+        s = s.masked_fill(col > row + ((Sk - Sq) if bottom_right else 0), float("-inf"))
     return torch.logsumexp(s, dim=-1)
 
 
