@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define MFA_B200_ABI_VERSION 2
+#define MFA_B200_ABI_VERSION 3
 
 /* error codes (0 == success).  mfa_last_error() returns the message of the last failure on the
  * calling thread. */
@@ -54,7 +54,7 @@ typedef struct mfa_params {
     int64_t o_batch_stride, o_head_stride, o_row_stride;
 
     int32_t is_causal;          /* top-left aligned: key col masked iff col > row (prefill.cuh:416) */
-    int32_t window_size_left;   /* accepted and ignored, like the reference (flash.h:33-34) */
+    int32_t window_size_left;   /* accepted and ignored, like the reference (flash.h:33-34), unless local_window */
     int32_t window_size_right;
 
     int32_t heads;              /* query heads */
@@ -95,6 +95,12 @@ typedef struct mfa_params {
      * col <= row + (len_k - len_q), per sequence (flash-attn >= 2.1 convention; what chunked prefill against a longer
      * cache needs).  0 = the reference's top-left mask (prefill.cuh:416).  New. */
     int32_t causal_bottom_right;
+    /* Prefill only: HONOUR window_size_left / window_size_right as a sliding-window (band) mask -- key col visible iff
+     * row + shift - left <= col <= row + shift + right, a bound < 0 absent, is_causal forcing right = 0; shift = 0
+     * (top-left, the reference's alignment) or len_k - len_q per sequence when causal_bottom_right is set (flash-attn's
+     * window_size convention).  KV tiles outside the band are skipped.  0 = the reference's behaviour: the two window
+     * fields are ignored (flash.h:33-34, README.md:153 "not implemented").  New. */
+    int32_t local_window;
 } mfa_params_t;
 
 /* --- introspection ------------------------------------------------------------------------ */

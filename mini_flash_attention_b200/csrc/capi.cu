@@ -147,7 +147,8 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     // head_dim in (64, 128] has two kernels: the single-CTA one (prefill_sm100.cu, default: faster today) and the
     // CTA-pair one (prefill_pair_sm100.cu; MFA_PREFILL_IMPL=pair or mfa_debug_set_prefill_impl(1) selects it).
     // (the opt-in pair kernel implements the reference's top-left mask only)
-    const bool use_pair = (dpad == 128) && (g_prefill_impl.load() == 1) && !(p->is_causal && p->causal_bottom_right);
+    const bool window = p->local_window && (p->window_size_left >= 0 || p->window_size_right >= 0);
+    const bool use_pair = (dpad == 128) && (g_prefill_impl.load() == 1) && !(p->is_causal && p->causal_bottom_right) && !window;
     const int kv_tile_box = use_pair ? 64 : mfa::kPrefillBlockN;
 
     CUtensorMap tmQ, tmK, tmV;
@@ -210,7 +211,13 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     kp.seqlen_q = p->seqlen_q;
     kp.seqlen_k = p->seqlen_k;
     kp.is_causal = p->is_causal ? 1 : 0;
-    kp.causal_br = (p->is_causal && p->causal_bottom_right) ? 1 : 0;
+    kp.causal_br = ((p->is_causal || window) && p->causal_bottom_right) ? 1 : 0;
+    // band mask: causal is the upper bound 0; window_size_left / right are honoured only with local_window (the
+    // reference accepts and ignores them, flash.h:33-34 / quirk Q10, and so do the plain entry points)
+    kp.has_hi = (p->is_causal || (window && p->window_size_right >= 0)) ? 1 : 0;
+    kp.win_right = p->is_causal ? 0 : (kp.has_hi ? p->window_size_right : 0);
+    kp.has_lo = (window && p->window_size_left >= 0) ? 1 : 0;
+    kp.win_left = kp.has_lo ? p->window_size_left : 0;
     const int rows_per_cta = mfa::prefill_rows_per_cta(dpad);
     kp.num_m_blocks = (p->seqlen_q + rows_per_cta - 1) / rows_per_cta;
     kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);   // api.cpp:99

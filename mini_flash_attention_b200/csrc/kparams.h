@@ -64,6 +64,11 @@ struct PrefillKParams {
     int32_t seqlen_q, seqlen_k;    // fixed lengths or max lengths
     int32_t is_causal;
     int32_t causal_br;             // causal mask aligned to the bottom-right corner: col <= row + (len_k - len_q)
+    // Band mask (sliding window): key col visible iff row + shift - win_left <= col <= row + shift +
+    // win_right, shift = causal_br ? len_k - len_q : 0; a bound < 0 is absent.  is_causal is folded into win_right = 0
+    // by the host, so the kernels only look at has_hi / has_lo.
+    int32_t has_hi, win_right;
+    int32_t has_lo, win_left;
     int32_t num_m_blocks;          // ceil(seqlen_q / 256)
     float scale, scale_log2;
     float* lse;                    // optional natural-log LSE: (B, H, Sq) fixed / (H, total_q) packed; -inf for empty rows

@@ -137,10 +137,15 @@ __device__ __forceinline__ uint64_t exp2_poly2(uint64_t x2) {
 
 // One work item = (m-block of kNQ*128 query rows, head, sequence).
 struct PrefillItem {
-    int h, b, kh, q_off, k_off, len_q, len_k, m0, n_max;
-    int shift;   // causal: key col visible iff col <= row + shift (0 = top-left like the reference, len_k - len_q = bottom-right)
-    int n_i[2];
+    int h, b, kh, q_off, k_off, len_q, len_k, m0;
+    // band mask: key col visible iff row + shift_lo <= col <= row + shift_hi (each bound only when p.has_lo / p.has_hi);
+    // causal is shift_hi = 0 (top-left like the reference) or len_k - len_q (bottom-right)
+    int shift_hi, shift_lo;
+    int lo_i[2], n_i[2];   // Q tile i works on KV tiles lo_i[i] <= j < n_i[i] (lo_i == n_i == 0: none)
+    int j_lo, n_max;       // the item's KV tile range: the union over its Q tiles
     bool valid;
+    __device__ __forceinline__ bool active(int i, int j) const { return j >= lo_i[i] && j < n_i[i]; }
+    __device__ __forceinline__ int count(int i) const { return n_i[i] - lo_i[i]; }
 };
 
 template <int kNQ>
@@ -148,7 +153,7 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
     PrefillItem w;
     const int mraw = item % p.num_m_blocks;
     const int rest = item / p.num_m_blocks;
-    const int mblk = p.is_causal ? (p.num_m_blocks - 1 - mraw) : mraw;   // causal: heaviest (largest m) blocks first
+    const int mblk = (p.has_hi && !p.has_lo) ? (p.num_m_blocks - 1 - mraw) : mraw;   // causal: heaviest (largest m) blocks first
     w.h = rest % p.heads;
     w.b = rest / p.heads;
     w.kh = w.h / p.group;
@@ -162,19 +167,33 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
         w.k_off = p.cu_seqlens_k[w.b];
         w.len_k = p.cu_seqlens_k[w.b + 1] - w.k_off;
     }
-    w.shift = p.causal_br ? (w.len_k - w.len_q) : 0;
+    const int shift = p.causal_br ? (w.len_k - w.len_q) : 0;
+    w.shift_hi = shift + p.win_right;
+    w.shift_lo = shift - p.win_left;
     w.m0 = mblk * (kNQ * kPrefillBlockM);
     w.valid = w.m0 < w.len_q;   // prefill.cuh:724-726: tiles past the sequence's own length do nothing
     const int n_tiles_k = (w.len_k + kPrefillBlockN - 1) / kPrefillBlockN;
     w.n_i[0] = w.n_i[1] = 0;
+    w.lo_i[0] = w.lo_i[1] = 0;
+    w.j_lo = 0x7fffffff;
+    w.n_max = 0;
 #pragma unroll
     for (int i = 0; i < kNQ; ++i) {
         const int r0 = w.m0 + i * kPrefillBlockM;
-        // causal: the tile's last row r0+127 sees cols <= r0+127+shift (none at all when that is negative)
-        if (r0 < w.len_q)
-            w.n_i[i] = p.is_causal ? min(n_tiles_k, max(0, (r0 + kPrefillBlockM + w.shift + kPrefillBlockN - 1) / kPrefillBlockN)) : n_tiles_k;
+        if (r0 < w.len_q) {
+            // upper bound: the tile's last row r0+127 sees cols <= r0+127+shift_hi (none at all when that is negative);
+            // lower bound: its first row r0 sees cols >= r0+shift_lo
+            const int hi = p.has_hi ? min(n_tiles_k, max(0, (r0 + kPrefillBlockM + w.shift_hi + kPrefillBlockN - 1) / kPrefillBlockN)) : n_tiles_k;
+            const int lo = p.has_lo ? max(0, r0 + w.shift_lo) / kPrefillBlockN : 0;
+            if (lo < hi) {
+                w.lo_i[i] = lo;
+                w.n_i[i] = hi;
+                w.j_lo = min(w.j_lo, lo);
+                w.n_max = max(w.n_max, hi);
+            }
+        }
     }
-    w.n_max = max(w.n_i[0], w.n_i[1]);
+    if (w.n_max == 0) w.j_lo = 0;
     return w;
 }
 
@@ -285,7 +304,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
             // batches TMA's out-of-bounds fill does it; for packed / paged K/V the producer warp zeroes them.
             const bool need_tail_fix = (bt != nullptr) || packed_k;
-            for (int j = 0; j < w.n_max; ++j) {
+            for (int j = w.j_lo; j < w.n_max; ++j) {
                 const int row0 = j * kBN;
                 const int rows_valid = min(w.len_k - row0, kBN);
 #pragma unroll 1
@@ -408,10 +427,10 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     tc_fence_after();
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i)
-                        if (w.n_i[i] > 0) issue_S(i, sK);
+                        if (w.active(i, w.j_lo)) issue_S(i, sK);
                     commit(&kv_empty[sK]);
                 }
-                for (int j = 0; j < n_max; ++j) {
+                for (int j = w.j_lo; j < n_max; ++j) {
                     const int sV = it % kStages;
                     mbar_wait(&kv_full[sV], (it / kStages) & 1);
                     ++it;
@@ -426,20 +445,20 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     MFA_TR(2, j, 0);
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i) {
-                        if (j < w.n_i[i]) {
-                            const uint32_t par = (t_cnt[i] + (uint32_t)j) & 1u;
+                        if (w.active(i, j)) {
+                            const uint32_t par = (t_cnt[i] + (uint32_t)(j - w.lo_i[i])) & 1u;
                             // (the first P.V of an item overwrites O_i: safe, because every softmax thread finished the
                             // previous item's epilogue -- its TMEM reads of O_i included -- before it released this P)
                             mbar_wait(&p_lo[i], par);
                             tc_fence_after();
                             MFA_TR(2, j, 1 + 3 * i);
-                            issue_PV(i, sV, j > 0, 0, kBN / 32, false);
+                            issue_PV(i, sV, j > w.lo_i[i], 0, kBN / 32, false);
                             mbar_wait(&p_hi[i], par);
                             tc_fence_after();
                             MFA_TR(2, j, 2 + 3 * i);
-                            issue_PV(i, sV, j > 0, kBN / 32, kBN / 16, true);
+                            issue_PV(i, sV, j > w.lo_i[i], kBN / 32, kBN / 16, true);
                         }
-                        if (j + 1 < w.n_i[i]) issue_S(i, sK);
+                        if (w.active(i, j + 1)) issue_S(i, sK);
                         MFA_TR(2, j, 3 + 3 * i);
                     }
                     commit(&kv_empty[sV]);
@@ -449,7 +468,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i) {
                     commit(&q_empty[i]);
-                    t_cnt[i] += (uint32_t)w.n_i[i];
+                    t_cnt[i] += (uint32_t)w.count(i);
                 }
                 ++q_cnt;
             }
@@ -474,11 +493,12 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
 #endif
             const int m0 = w.m0, len_k = w.len_k, len_q = w.len_q;
             const int qrow = m0 + i * kBM + row_in_tile;            // row inside the sequence
-            const int n_mine = w.n_i[i];
+            const int j_first = w.lo_i[i];
+            const int n_mine = w.count(i);
             float m_run = -INFINITY, l_run = 0.f;
 
-            for (int j = 0; j < n_mine; ++j) {
-                const uint32_t par = (t_cnt + (uint32_t)j) & 1u;
+            for (int j = j_first; j < w.n_i[i]; ++j) {
+                const uint32_t par = (t_cnt + (uint32_t)(j - j_first)) & 1u;
                 MFA_TR(i, j, 0);
                 mbar_wait(&s_full[i], par);
                 tc_fence_after();
@@ -490,12 +510,18 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 MFA_TR(i, j, 2);
 
                 const int col0 = j * kBN;
-                const bool need_mask = (col0 + kBN > len_k) || (p.is_causal && (col0 + kBN - 1 > m0 + i * kBM + w.shift));
+                const bool need_mask = (col0 + kBN > len_k) || (p.has_hi && (col0 + kBN - 1 > m0 + i * kBM + w.shift_hi));
                 if (need_mask) {
-                    const int lim = p.is_causal ? min(len_k, qrow + 1 + w.shift) : len_k;   // cols >= lim are masked
+                    const int lim = p.has_hi ? min(len_k, qrow + 1 + w.shift_hi) : len_k;   // cols >= lim are masked
 #pragma unroll
                     for (int c = 0; c < 128; ++c)
                         if (col0 + c >= lim) su[c] = 0xff800000u;   // -inf
+                }
+                if (p.has_lo && col0 < m0 + i * kBM + kBM - 1 + w.shift_lo) {   // the tile's last row has the largest bound
+                    const int lim_lo = qrow + w.shift_lo;   // cols < lim_lo are masked
+#pragma unroll
+                    for (int c = 0; c < 128; ++c)
+                        if (col0 + c < lim_lo) su[c] = 0xff800000u;
                 }
                 // row max: 8 independent 3-input max chains, then a tree
                 float mx[8];
@@ -516,7 +542,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
                 m_run = m_use;
 
-                if (j > 0 && __any_sync(0xffffffffu, grow)) {
+                if (j > j_first && __any_sync(0xffffffffu, grow)) {
                     // O_i currently holds sum_{t<j} P_t V_t: wait for PV(j-1), then rescale our row in place.
                     // Must happen before any part of P(j) is released to the MMA warp.
                     mbar_wait(&o_full[i], par ^ 1u);
@@ -656,7 +682,7 @@ static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& t
     long long ctas = items;
     if (!non_persistent && p.cu_seqlens_q == nullptr && items > sms) {
         ctas = sms;
-        if (p.is_causal) {
+        if (p.has_hi) {
             auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };
             while (ctas > 1 && gcd(ctas, p.num_m_blocks) != 1) --ctas;
         }
