@@ -71,7 +71,7 @@ def _i32_ptr(t: Optional[torch.Tensor]) -> Optional[int]:
 
 
 def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, window_size_right, _want_lse=False,
-                                 _bottom_right=False):
+                                 _bottom_right=False, _local_window=False):
     """Fixed-length prefill.  q (B,Sq,H,D); k, v (B,Sk,Hkv,D); returns (B,Sq,H,D).  api.cpp:113-186.
     With _want_lse (the `_lse` entry point) also the natural-log LSE (B,H,Sq) fp32."""
     _check_qkv(q, k, v)
@@ -106,6 +106,7 @@ def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, wind
     P.o_batch_stride, P.o_row_stride, P.o_head_stride = oc.stride(0), oc.stride(1), oc.stride(2)
     P.is_causal = int(bool(is_causal))  # api.cpp:157, :88
     P.causal_bottom_right = int(bool(_bottom_right))  # new; 0 = the reference's top-left mask
+    P.local_window = int(bool(_local_window))  # new; 0 = window sizes ignored like the reference
     P.window_size_left, P.window_size_right = int(window_size_left), int(window_size_right)
     P.heads, P.kv_heads, P.batch = num_heads, kv_num_heads, batch
     P.seqlen_q, P.seqlen_k, P.head_dim = seqlen_q, seqlen_k, head_dim
@@ -121,7 +122,7 @@ def mini_flash_attention_forward(q, k, v, out, is_causal, window_size_left, wind
 
 def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal,
                                         window_size_left, window_size_right, block_table, _want_lse=False,
-                                        _bottom_right=False):
+                                        _bottom_right=False, _local_window=False):
     """Packed variable-length prefill, optionally with paged K/V.  api.cpp:189-267.
 
     q (total_q,H,D); k, v (total_k,Hkv,D) or, with block_table (batch,max_blocks) int32,
@@ -178,6 +179,7 @@ def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max
     P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1)
     P.is_causal = int(bool(causal))  # api.cpp:231
     P.causal_bottom_right = int(bool(_bottom_right))
+    P.local_window = int(bool(_local_window))
     P.window_size_left, P.window_size_right = int(window_size_left), int(window_size_right)
     P.heads, P.kv_heads, P.batch = num_heads, kv_num_heads, batch
     P.seqlen_q, P.seqlen_k, P.head_dim = int(max_seqlen_q), int(max_seqlen_k), head_dim
@@ -382,16 +384,19 @@ def mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, bl
     return _py_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits, _want_lse=True)
 
 
-# superset entry points: optional LSE; causal mask aligned bottom-right; in-place k/v append before the decode
+# superset entry points: optional LSE; mask aligned bottom-right; window sizes HONOURED (sliding window); in-place k/v
+# append before the decode
 def mini_flash_attention_forward_ext(q, k, v, out, is_causal, window_size_left, window_size_right, return_lse, bottom_right):
-    r = _py_forward(q, k, v, out, is_causal, window_size_left, window_size_right, _want_lse=return_lse, _bottom_right=bottom_right)
+    r = _py_forward(q, k, v, out, is_causal, window_size_left, window_size_right, _want_lse=return_lse, _bottom_right=bottom_right,
+                    _local_window=True)
     return r if return_lse else (r, None)
 
 
 def mini_flash_attention_varlen_forward_ext(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal,
                                             window_size_left, window_size_right, block_table, return_lse, bottom_right):
     r = _py_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, window_size_left,
-                           window_size_right, block_table, _want_lse=return_lse, _bottom_right=bottom_right)
+                           window_size_right, block_table, _want_lse=return_lse, _bottom_right=bottom_right,
+                           _local_window=True)
     return r if return_lse else (r, None)
 
 

@@ -63,7 +63,7 @@ void* stream_of(const at::Tensor& t) { return at::cuda::getCurrentCUDAStream(t.g
 static std::tuple<at::Tensor, at::Tensor> forward_impl(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v,
                                                        const std::optional<at::Tensor>& out_, bool is_causal,
                                                        int64_t window_left, int64_t window_right, bool want_lse,
-                                                       bool bottom_right = false) {
+                                                       bool bottom_right = false, bool local_window = false) {
     check_qkv(q, k, v);
     TORCH_CHECK(q.dim() == 4 && k.dim() == 4 && v.dim() == 4, "q, k, v must be 4-D (batch, seqlen, heads, head_dim)");
     const int64_t batch = q.size(0), seqlen_q = q.size(1), heads = q.size(2), head_dim = q.size(3);
@@ -102,6 +102,7 @@ static std::tuple<at::Tensor, at::Tensor> forward_impl(const at::Tensor& q, cons
     P.o_batch_stride = oc.stride(0); P.o_row_stride = oc.stride(1); P.o_head_stride = oc.stride(2);
     P.is_causal = is_causal ? 1 : 0;   // api.cpp:157, :88
     P.causal_bottom_right = bottom_right ? 1 : 0;   // new; 0 = the reference's top-left mask
+    P.local_window = local_window ? 1 : 0;          // new; 0 = window sizes ignored like the reference
     P.window_size_left = (int32_t)window_left; P.window_size_right = (int32_t)window_right;
     P.heads = (int32_t)heads; P.kv_heads = (int32_t)kv_heads; P.batch = (int32_t)batch;
     P.seqlen_q = (int32_t)seqlen_q; P.seqlen_k = (int32_t)seqlen_k; P.head_dim = (int32_t)head_dim;
@@ -123,11 +124,11 @@ std::tuple<at::Tensor, at::Tensor> mini_flash_attention_forward_lse(const at::Te
                                                                     int64_t window_right) {
     return forward_impl(q, k, v, out_, is_causal, window_left, window_right, true);
 }
-// superset entry point: optional LSE, causal mask aligned bottom-right
+// superset entry point: optional LSE, mask aligned bottom-right, window_left / window_right HONOURED (sliding window)
 std::tuple<at::Tensor, std::optional<at::Tensor>> mini_flash_attention_forward_ext(
     const at::Tensor& q, const at::Tensor& k, const at::Tensor& v, std::optional<at::Tensor> out_, bool is_causal,
     int64_t window_left, int64_t window_right, bool return_lse, bool bottom_right) {
-    auto r = forward_impl(q, k, v, out_, is_causal, window_left, window_right, return_lse, bottom_right);
+    auto r = forward_impl(q, k, v, out_, is_causal, window_left, window_right, return_lse, bottom_right, true);
     return {std::get<0>(r), return_lse ? std::optional<at::Tensor>(std::get<1>(r)) : std::nullopt};
 }
 
@@ -139,7 +140,7 @@ static std::tuple<at::Tensor, at::Tensor> varlen_impl(const at::Tensor& q, const
                                                       int64_t max_seqlen_q, int64_t max_seqlen_k, bool causal,
                                                       int64_t window_left, int64_t window_right,
                                                       const std::optional<at::Tensor>& block_table, bool want_lse,
-                                                      bool bottom_right = false) {
+                                                      bool bottom_right = false, bool local_window = false) {
     check_qkv(q, k, v);
     TORCH_CHECK(cu_seqlens_q.is_cuda(), "cu_seqlens_q must be on CUDA");
     TORCH_CHECK(cu_seqlens_k.is_cuda(), "cu_seqlens_k must be on CUDA");
@@ -197,6 +198,7 @@ static std::tuple<at::Tensor, at::Tensor> varlen_impl(const at::Tensor& q, const
     P.o_row_stride = out.stride(0); P.o_head_stride = out.stride(1);
     P.is_causal = causal ? 1 : 0;   // api.cpp:231
     P.causal_bottom_right = bottom_right ? 1 : 0;
+    P.local_window = local_window ? 1 : 0;
     P.window_size_left = (int32_t)window_left; P.window_size_right = (int32_t)window_right;
     P.heads = (int32_t)heads; P.kv_heads = (int32_t)kv_heads; P.batch = (int32_t)batch;
     P.seqlen_q = (int32_t)max_seqlen_q; P.seqlen_k = (int32_t)max_seqlen_k; P.head_dim = (int32_t)head_dim;
@@ -232,7 +234,7 @@ std::tuple<at::Tensor, std::optional<at::Tensor>> mini_flash_attention_varlen_fo
     const at::Tensor& cu_seqlens_k, int64_t max_seqlen_q, int64_t max_seqlen_k, bool causal, int64_t window_left,
     int64_t window_right, std::optional<at::Tensor> block_table, bool return_lse, bool bottom_right) {
     auto r = varlen_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, window_left,
-                         window_right, block_table, return_lse, bottom_right);
+                         window_right, block_table, return_lse, bottom_right, true);
     return {std::get<0>(r), return_lse ? std::optional<at::Tensor>(std::get<1>(r)) : std::nullopt};
 }
 

@@ -6,11 +6,16 @@ Each function is, like in the reference, a one-line positional forward into the 
 """
 from __future__ import annotations
 
-from typing import Optional, Union
+from typing import Optional, Tuple, Union
 
 import torch
 
 from . import _C
+
+
+def _window(window_size) -> Tuple[int, int]:
+    wl, wr = window_size
+    return (int(wl) if wl is not None and wl >= 0 else -1), (int(wr) if wr is not None and wr >= 0 else -1)
 
 
 def flash_attn_func(
@@ -21,6 +26,7 @@ def flash_attn_func(
     *,
     return_lse: bool = False,
     bottom_right: bool = False,
+    window_size: Tuple[int, int] = (-1, -1),
 ):
     """FlashAttention forward (reference: interface.py:6-37).
 
@@ -38,12 +44,18 @@ def flash_attn_func(
             >= 2.1 convention and what a chunk of new queries against a longer cache needs.  Default off = reference.
         return_lse: (keyword-only, new -- SURVEY 8f row 1) also return the row-wise log-sum-exp of the scaled scores,
             which the reference computes and drops; makes the op composable (chunked / ring prefill merges).
+        window_size: (keyword-only, new -- SURVEY 8f row 3; the reference plumbs window sizes but never implements
+            them, flash.h:33-34, README.md:153) sliding-window attention ``(left, right)``: key j is visible to query i
+            iff ``i + s - left <= j <= i + s + right`` with s = 0 (top-left, the reference's alignment) or
+            ``seqlen_k - seqlen_q`` with bottom_right=True (flash-attn's convention); -1 = unbounded; causal=True
+            forces right = 0.  KV tiles outside the band are skipped, so cost scales with the window, not seqlen_k.
     Return:
         out: (batch_size, seqlen_q, nheads, headdim)
         softmax_lse [if return_lse]: (batch_size, nheads, seqlen_q) fp32, natural log; -inf for rows that see no key
     """
-    if bottom_right:
-        out, lse = _C.mini_flash_attention_forward_ext(q, k, v, None, causal, -1, -1, return_lse, True)
+    wl, wr = _window(window_size)
+    if bottom_right or wl >= 0 or wr >= 0:
+        out, lse = _C.mini_flash_attention_forward_ext(q, k, v, None, causal, wl, wr, return_lse, bottom_right)
         return (out, lse) if return_lse else out
     if return_lse:
         return _C.mini_flash_attention_forward_lse(q, k, v, None, causal, -1, -1)
@@ -63,6 +75,7 @@ def flash_attn_varlen_func(
     *,
     return_lse: bool = False,
     bottom_right: bool = False,
+    window_size: Tuple[int, int] = (-1, -1),
 ):
     """FlashAttention forward for packed variable-length batches (reference: interface.py:40-92).
 
@@ -77,13 +90,16 @@ def flash_attn_varlen_func(
             (any page size that is a multiple of 8), not per 64-row tile.
         return_lse: (keyword-only, new) also return the log-sum-exp, see flash_attn_func
         bottom_right: (keyword-only, new) bottom-right aligned causal mask per sequence, see flash_attn_func
+        window_size: (keyword-only, new) sliding window (left, right) per sequence, see flash_attn_func
     Return:
         out: (total_q, nheads, headdim)
         softmax_lse [if return_lse]: (nheads, total_q) fp32
     """
-    if bottom_right:
+    wl, wr = _window(window_size)
+    if bottom_right or wl >= 0 or wr >= 0:
         out, lse = _C.mini_flash_attention_varlen_forward_ext(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
-                                                              max_seqlen_k, causal, -1, -1, block_table, return_lse, True)
+                                                              max_seqlen_k, causal, wl, wr, block_table, return_lse,
+                                                              bottom_right)
         return (out, lse) if return_lse else out
     fn = _C.mini_flash_attention_varlen_forward_lse if return_lse else _C.mini_flash_attention_varlen_forward
     return fn(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, causal, -1, -1, block_table)

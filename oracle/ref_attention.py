@@ -34,9 +34,28 @@ def _expand_kv(x: torch.Tensor, group: int, dim: int) -> torch.Tensor:
     return x if group == 1 else x.repeat_interleave(group, dim=dim)
 
 
-def attention_ref(q, k, v, causal: bool = False, key_len: Optional[int] = None, bottom_right: bool = False) -> torch.Tensor:
+def _band_mask(s, Sq, Sk, causal, bottom_right, window_size):
+    """-inf outside row + shift - left <= col <= row + shift + right (a bound < 0 absent; causal => right = 0);
+    shift = 0 (top-left, the reference's prefill.cuh:416) or Sk - Sq (bottom_right, flash-attn's convention)."""
+    wl, wr = window_size
+    if causal:
+        wr = 0
+    if wl < 0 and wr < 0:
+        return s
+    row = torch.arange(Sq, device=s.device)[:, None] + ((Sk - Sq) if bottom_right else 0)
+    col = torch.arange(Sk, device=s.device)[None, :]
+    if wr >= 0:
+        s = s.masked_fill(col > row + wr, float("-inf"))
+    if wl >= 0:
+        s = s.masked_fill(col < row - wl, float("-inf"))
+    return s
+
+
+def attention_ref(q, k, v, causal: bool = False, key_len: Optional[int] = None, bottom_right: bool = False,
+                  window_size=(-1, -1)) -> torch.Tensor:
     """q (B,Sq,H,D), k/v (B,Sk,Hkv,D) -> (B,Sq,H,D) float32.  Top-left causal (col > row masked, the reference's
-    prefill.cuh:416) or, with bottom_right, col > row + (Sk - Sq) masked (flash-attn >= 2.1)."""
+    prefill.cuh:416) or, with bottom_right, col > row + (Sk - Sq) masked (flash-attn >= 2.1).
+    window_size: sliding-window band (no reference implementation: fp32 math only, parity unpinned)."""
     B, Sq, H, D = q.shape
     Sk, Hkv = k.shape[1], k.shape[2]
     qf = q.float().permute(0, 2, 1, 3)
@@ -45,17 +64,14 @@ def attention_ref(q, k, v, causal: bool = False, key_len: Optional[int] = None, 
     s = torch.matmul(qf, kf.transpose(-1, -2)) * (1.0 / math.sqrt(D))
     if key_len is not None and key_len < Sk:
         s[..., key_len:] = float("-inf")
-    if causal:
-        row = torch.arange(Sq, device=q.device)[:, None]
-        col = torch.arange(Sk, device=q.device)[None, :]
-        s = s.masked_fill(col > row + ((Sk - Sq) if bottom_right else 0), float("-inf"))
+    s = _band_mask(s, Sq, Sk, causal, bottom_right, window_size)
     p = torch.softmax(s, dim=-1)
     p = torch.nan_to_num(p, nan=0.0)  # fully masked rows => 0 output (prefill.cuh:604-605)
     o = torch.matmul(p, vf)
     return o.permute(0, 2, 1, 3).contiguous()
 
 
-def lse_ref(q, k, causal: bool = False, bottom_right: bool = False) -> torch.Tensor:
+def lse_ref(q, k, causal: bool = False, bottom_right: bool = False, window_size=(-1, -1)) -> torch.Tensor:
     """Row-wise natural-log LSE of the scaled, masked scores: q (B,Sq,H,D), k (B,Sk,Hkv,D) -> (B,H,Sq) float32;
     -inf where a row sees no key.  (The quantity the reference stores in softmax_lse, decode.cuh:750-754.)"""
     B, Sq, H, D = q.shape
@@ -63,10 +79,7 @@ def lse_ref(q, k, causal: bool = False, bottom_right: bool = False) -> torch.Ten
     qf = q.float().permute(0, 2, 1, 3)
     kf = _expand_kv(k.float(), H // Hkv, 2).permute(0, 2, 1, 3)
     s = torch.matmul(qf, kf.transpose(-1, -2)) * (1.0 / math.sqrt(D))
-    if causal:
-        row = torch.arange(Sq, device=q.device)[:, None]
-        col = torch.arange(Sk, device=q.device)[None, :]
-        s = s.masked_fill(col > row + ((Sk - Sq) if bottom_right else 0), float("-inf"))
+    s = _band_mask(s, Sq, Sk, causal, bottom_right, window_size)
     return torch.logsumexp(s, dim=-1)
 
 
@@ -78,7 +91,8 @@ def gather_paged(cache: torch.Tensor, block_table_row: torch.Tensor, length: int
     return cache[idx].reshape(n_pages * page, cache.shape[2], cache.shape[3])[:length]
 
 
-def varlen_ref(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, block_table=None) -> torch.Tensor:
+def varlen_ref(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, block_table=None, bottom_right=False,
+               window_size=(-1, -1)) -> torch.Tensor:
     """Packed varlen: q (total_q,H,D); k/v (total_k,Hkv,D) or paged (num_blocks,page,Hkv,D)."""
     out = torch.zeros(q.shape, dtype=torch.float32, device=q.device)
     cq = cu_seqlens_q.tolist()
@@ -96,7 +110,8 @@ def varlen_ref(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, block_table=No
             vb = v[ck[b]:ck[b + 1]][None]
         if lk == 0:
             continue
-        out[cq[b]:cq[b + 1]] = attention_ref(qb, kb, vb, causal=causal)[0]
+        out[cq[b]:cq[b + 1]] = attention_ref(qb, kb, vb, causal=causal, bottom_right=bottom_right,
+                                             window_size=window_size)[0]
     return out
 
 

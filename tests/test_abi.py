@@ -25,7 +25,7 @@ def test_library_exports_every_header_symbol(mfa_lib):
     for s in syms:
         assert hasattr(mfa_lib, s), f"{s} declared in include/mfa_b200.h but not exported"
     assert sorted(_lib.EXPORTS) == syms
-    assert mfa_lib.mfa_abi_version() == 2
+    assert mfa_lib.mfa_abi_version() == 3
 
 
 def test_params_struct_matches_header_layout(mfa_lib):
@@ -41,7 +41,7 @@ int main(void) {
   printf("%zu %zu %zu %zu %zu %zu\n", sizeof(mfa_params_t), offsetof(mfa_params_t, is_causal),
          offsetof(mfa_params_t, softmax_scale), offsetof(mfa_params_t, cu_seqlens_q),
          offsetof(mfa_params_t, k_cache_block_stride), offsetof(mfa_params_t, partial_out));
-  printf("%zu %zu %zu %zu %zu\n", offsetof(mfa_params_t, causal_bottom_right), sizeof(mfa_append_params_t),
+  printf("%zu %zu %zu %zu %zu %zu\n", offsetof(mfa_params_t, local_window), offsetof(mfa_params_t, causal_bottom_right), sizeof(mfa_append_params_t),
          offsetof(mfa_append_params_t, k_cache), offsetof(mfa_append_params_t, seqlens_out),
          offsetof(mfa_append_params_t, is_bf16));
   return 0; }
@@ -55,7 +55,7 @@ int main(void) {
     from mini_flash_attention_b200._lib import MfaAppendParams as A
     assert vals == [ctypes.sizeof(MfaParams), MfaParams.is_causal.offset, MfaParams.softmax_scale.offset,
                     MfaParams.cu_seqlens_q.offset, MfaParams.k_cache_block_stride.offset, MfaParams.partial_out.offset,
-                    MfaParams.causal_bottom_right.offset, ctypes.sizeof(A), A.k_cache.offset, A.seqlens_out.offset,
+                    MfaParams.local_window.offset, MfaParams.causal_bottom_right.offset, ctypes.sizeof(A), A.k_cache.offset, A.seqlens_out.offset,
                     A.is_bf16.offset]
 
 
@@ -71,10 +71,10 @@ def test_python_surface_matches_reference():
     import mini_flash_attention as m
     assert m.__all__ == ["flash_attn_func", "flash_attn_varlen_func", "flash_attn_with_kvcache"]
     assert positional(m.flash_attn_func) == ["q", "k", "v", "causal"]
-    assert kw_only(m.flash_attn_func) == {"return_lse": False, "bottom_right": False}
+    assert kw_only(m.flash_attn_func) == {"return_lse": False, "bottom_right": False, "window_size": (-1, -1)}
     assert positional(m.flash_attn_varlen_func) == [
         "q", "k", "v", "cu_seqlens_q", "cu_seqlens_k", "max_seqlen_q", "max_seqlen_k", "causal", "block_table"]
-    assert kw_only(m.flash_attn_varlen_func) == {"return_lse": False, "bottom_right": False}
+    assert kw_only(m.flash_attn_varlen_func) == {"return_lse": False, "bottom_right": False, "window_size": (-1, -1)}
     sig = inspect.signature(m.flash_attn_with_kvcache)
     assert positional(m.flash_attn_with_kvcache) == ["q", "k_cache", "v_cache", "cache_seqlens", "block_table", "num_splits"]
     assert kw_only(m.flash_attn_with_kvcache) == {"causal": False, "return_lse": False, "k": None, "v": None}
