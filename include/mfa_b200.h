@@ -162,6 +162,34 @@ int mfa_combine_partials(const float* packed, int num_partials, int rows, int he
                          void* out, int64_t out_row_stride, int is_bf16, float* lse_out,
                          void* cuda_stream);
 
+/* --- KV-sharded decode with the exchange fused into the merge kernel over NVLink peer memory (no reference
+ *     analogue -- the reference is single-GPU).  Every rank owns a slice of the KV axis of every sequence; q is
+ *     replicated.  mfa_decode_fwd_kv_sharded launches the split-KV kernel over the local rows and then ONE kernel that
+ *     merges the local splits, pushes the normalised row + LSE into every peer's gather buffer (P2P stores + release
+ *     flag), waits for the peers' rows and writes the final output (p->o_ptr, out dtype; optional p->softmax_lse_ptr):
+ *     no NCCL call, no host synchronisation.  All ranks must call it the same number of times, in the same order.
+ *   mfa_xchg_create:  allocates this rank's gather buffer (cudaMalloc on the current device), max_rows >= batch*heads
+ *   mfa_xchg_export:  writes the MFA_XCHG_HANDLE_BYTES-byte IPC handle of that buffer (exchange it out of band, e.g.
+ *                     with torch.distributed.all_gather_object)
+ *   mfa_xchg_connect: handles = world x MFA_XCHG_HANDLE_BYTES bytes in rank order (cudaIpcOpenMemHandle per peer)
+ *   mfa_xchg_connect_ptrs: the same with raw device pointers (ranks that live in ONE process; tests)
+ *   mfa_xchg_local_ptr: the local buffer's device pointer (for mfa_xchg_connect_ptrs)
+ *   mfa_xchg_status:  0, or 1 + the rank whose push did not arrive within the timeout (synchronises the device)
+ *   mfa_decode_kv_sharded_workspace_bytes: scratch for num_splits (>= 1) splits: splits * batch*heads * (D+1) floats */
+#define MFA_XCHG_HANDLE_BYTES 64
+#define MFA_XCHG_MAX_WORLD 8
+typedef struct mfa_xchg mfa_xchg_t;
+int    mfa_xchg_create(int world, int rank, int max_rows, int head_dim, mfa_xchg_t** out);
+int    mfa_xchg_export(mfa_xchg_t* x, void* handle_out);
+int    mfa_xchg_connect(mfa_xchg_t* x, const void* handles);
+int    mfa_xchg_connect_ptrs(mfa_xchg_t* x, void* const* peer_ptrs);
+void*  mfa_xchg_local_ptr(mfa_xchg_t* x);
+int    mfa_xchg_status(mfa_xchg_t* x);
+int    mfa_xchg_destroy(mfa_xchg_t* x);
+size_t mfa_decode_kv_sharded_workspace_bytes(const mfa_params_t* p, int num_splits);
+int    mfa_decode_fwd_kv_sharded(const mfa_params_t* p, void* workspace, size_t workspace_bytes, mfa_xchg_t* x,
+                                 void* cuda_stream);
+
 /* tuning aid: libraries built with -DMFA_TRACE write clock64() stamps of prefill CTA (0,0,0) into this device
  * buffer ([3 roles][64 iterations][8 events] int64); a no-op in normal builds.  NULL disables. */
 void mfa_debug_set_trace(void* device_buffer);

@@ -337,6 +337,33 @@ def decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits=0
     return o, lse
 
 
+def decode_kv_sharded_fused(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, xchg_handle: int,
+                            return_lse: bool = False):
+    """KV-sharded decode with the exchange fused into the merge kernel (include/mfa_b200.h, csrc/xchg_sm100.cu): this
+    rank's rows of the KV axis in, the FULL result (B,1,H,D) in q's dtype out on every rank -- split-KV kernel, then one
+    kernel that merges the local splits, pushes the row to the peers over NVLink, waits for theirs and merges.  No NCCL
+    call.  `xchg_handle` is a connected mfa_xchg_t* (parallel.KVShardExchange).  New; no reference analogue."""
+    P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
+    batch, _, num_heads, head_dim = q.shape
+    _check(P.seqlen_k > 0 and q.numel() > 0, "KV-sharded decode needs a non-empty problem")
+    out = torch.empty(q.shape, dtype=q.dtype, device=q.device)
+    lse = torch.empty(batch, num_heads, dtype=torch.float32, device=q.device) if return_lse else None
+    P.o_ptr = out.data_ptr()
+    P.o_batch_stride, P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
+    if return_lse:
+        P.softmax_lse_ptr = lse.data_ptr()
+    lib = _lib.load()
+    with torch.cuda.device(q.device):
+        splits = lib.mfa_decode_num_splits(ctypes.byref(P))
+        _check(splits >= 1, "mfa_decode_num_splits failed")
+        P.num_splits = splits
+        ws_bytes = lib.mfa_decode_kv_sharded_workspace_bytes(ctypes.byref(P), splits)
+        ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=q.device)
+        _lib.check(lib.mfa_decode_fwd_kv_sharded(ctypes.byref(P), ws.data_ptr(), ws_bytes, xchg_handle,
+                                                 _stream_ptr(q.device)), "mfa_decode_fwd_kv_sharded")
+    return (out, lse) if return_lse else out
+
+
 def combine_partials(packed: torch.Tensor, out_dtype: torch.dtype, return_lse: bool = False):
     """LSE merge of R packed partials (R, rows, D+1) fp32 -> (rows, D) out_dtype.  decode.cuh:665-755."""
     _check(packed.is_cuda and packed.dtype == torch.float32 and packed.dim() == 3, "packed must be a CUDA fp32 (R, rows, D+1) tensor")

@@ -66,7 +66,11 @@ EXPORTS = (
     "mfa_abi_version", "mfa_last_error", "mfa_device_supported", "mfa_prefill_fwd", "mfa_decode_num_splits",
     "mfa_decode_workspace_bytes", "mfa_decode_fwd", "mfa_combine_partials", "mfa_launch_count", "mfa_selftest_umma",
     "mfa_debug_set_trace", "mfa_selftest_umma2", "mfa_debug_set_prefill_impl", "mfa_kvcache_append",
+    "mfa_xchg_create", "mfa_xchg_export", "mfa_xchg_connect", "mfa_xchg_connect_ptrs", "mfa_xchg_local_ptr",
+    "mfa_xchg_status", "mfa_xchg_destroy", "mfa_decode_kv_sharded_workspace_bytes", "mfa_decode_fwd_kv_sharded",
 )
+XCHG_HANDLE_BYTES = 64
+XCHG_MAX_WORLD = 8
 
 _lib = None
 
@@ -102,6 +106,24 @@ def load() -> ctypes.CDLL:
     lib.mfa_launch_count.restype = ctypes.c_uint64
     lib.mfa_kvcache_append.argtypes = [ctypes.POINTER(MfaAppendParams), ctypes.c_void_p]
     lib.mfa_kvcache_append.restype = ctypes.c_int
+    lib.mfa_xchg_create.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
+    lib.mfa_xchg_create.restype = ctypes.c_int
+    lib.mfa_xchg_export.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    lib.mfa_xchg_export.restype = ctypes.c_int
+    lib.mfa_xchg_connect.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    lib.mfa_xchg_connect.restype = ctypes.c_int
+    lib.mfa_xchg_connect_ptrs.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+    lib.mfa_xchg_connect_ptrs.restype = ctypes.c_int
+    lib.mfa_xchg_local_ptr.argtypes = [ctypes.c_void_p]
+    lib.mfa_xchg_local_ptr.restype = ctypes.c_void_p
+    lib.mfa_xchg_status.argtypes = [ctypes.c_void_p]
+    lib.mfa_xchg_status.restype = ctypes.c_int
+    lib.mfa_xchg_destroy.argtypes = [ctypes.c_void_p]
+    lib.mfa_xchg_destroy.restype = ctypes.c_int
+    lib.mfa_decode_kv_sharded_workspace_bytes.argtypes = [P, ctypes.c_int]
+    lib.mfa_decode_kv_sharded_workspace_bytes.restype = ctypes.c_size_t
+    lib.mfa_decode_fwd_kv_sharded.argtypes = [P, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+    lib.mfa_decode_fwd_kv_sharded.restype = ctypes.c_int
     lib.mfa_debug_set_trace.argtypes = [ctypes.c_void_p]
     lib.mfa_debug_set_trace.restype = None
     lib.mfa_debug_set_prefill_impl.argtypes = [ctypes.c_int]

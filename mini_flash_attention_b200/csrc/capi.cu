@@ -27,7 +27,21 @@ int prefill_rows_per_cta(int dpad);
 cudaError_t launch_prefill_pair(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                 const PrefillKParams& p, bool is_bf16, cudaStream_t stream);
 cudaError_t launch_kvcache_append(const mfa_append_params_t& p, int sm_count, cudaStream_t stream);
+cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream);
 }  // namespace mfa
+
+// Exchange buffer of the KV-sharded decode (include/mfa_b200.h; kernel in xchg_sm100.cu).  One cudaMalloc per rank:
+//   floats [2 parities][world][max_rows][head_dim + 4]  |  uint32 flags [world][max_rows]  |  uint32 status[4]
+struct mfa_xchg {
+    int world, rank, max_rows, head_dim, device;
+    size_t data_bytes, flag_bytes, bytes;
+    void* local;
+    void* peer[MFA_XCHG_MAX_WORLD];
+    bool ipc_opened[MFA_XCHG_MAX_WORLD];
+    bool connected;
+    uint32_t epoch;
+    long long timeout_cycles;
+};
 
 namespace {
 
@@ -278,7 +292,25 @@ size_t mfa_decode_workspace_bytes(const mfa_params_t* p, int num_splits) {
     return (size_t)num_splits * rows * ((size_t)p->head_dim + 1) * sizeof(float);   // api.cpp:333-334
 }
 
+static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_bytes, mfa_xchg_t* x, void* cuda_stream);
+
 int mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    return decode_impl(p, workspace, workspace_bytes, nullptr, cuda_stream);
+}
+
+size_t mfa_decode_kv_sharded_workspace_bytes(const mfa_params_t* p, int num_splits) {
+    if (!p) return 0;
+    const size_t rows = (size_t)p->batch * (size_t)p->heads;
+    return (size_t)std::max(1, num_splits) * rows * ((size_t)p->head_dim + 1) * sizeof(float);
+}
+
+int mfa_decode_fwd_kv_sharded(const mfa_params_t* p, void* workspace, size_t workspace_bytes, mfa_xchg_t* x,
+                              void* cuda_stream) {
+    if (!x) return fail(MFA_ERR_INVALID_ARG, "null exchange");
+    return decode_impl(p, workspace, workspace_bytes, x, cuda_stream);
+}
+
+static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_bytes, mfa_xchg_t* x, void* cuda_stream) {
     int rc = check_common(p);
     if (rc) return rc;
     if ((rc = check_device())) return rc;
@@ -300,7 +332,16 @@ int mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_byte
     const int dpad = dpad_of(D);
     const bool bf16 = p->is_bf16 != 0;
     const int splits = decode_splits_for(p);
-    const size_t need = mfa_decode_workspace_bytes(p, splits);
+    if (x) {
+        if (!x->connected) return fail(MFA_ERR_INVALID_ARG, "exchange is not connected (mfa_xchg_connect)");
+        if (p->partial_out) return fail(MFA_ERR_INVALID_ARG, "partial_out and a fused exchange exclude each other");
+        if (p->head_dim != x->head_dim || (int64_t)p->batch * p->heads > x->max_rows)
+            return fail(MFA_ERR_INVALID_ARG, "exchange was created for head_dim %d, max_rows %d", x->head_dim, x->max_rows);
+        int dev = -1;
+        cudaGetDevice(&dev);
+        if (dev != x->device) return fail(MFA_ERR_INVALID_ARG, "exchange lives on device %d, current device is %d", x->device, dev);
+    }
+    const size_t need = x ? mfa_decode_kv_sharded_workspace_bytes(p, splits) : mfa_decode_workspace_bytes(p, splits);
     if (need > 0 && (!workspace || workspace_bytes < need))
         return fail(MFA_ERR_INVALID_ARG, "decode workspace too small: need %zu bytes for %d splits, got %zu", need, splits,
                     workspace_bytes);
@@ -342,6 +383,10 @@ int mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_byte
     kp.lse = p->softmax_lse_ptr;
     kp.o_part = splits > 1 ? static_cast<float*>(workspace) : nullptr;
     kp.lse_part = splits > 1 ? static_cast<float*>(workspace) + (size_t)splits * rows * D : nullptr;
+    if (x && splits == 1) {   // one split: the kernel writes its normalised fp32 partial straight into the workspace
+        kp.o = workspace;
+        kp.lse = static_cast<float*>(workspace) + rows * D;
+    }
     kp.q_batch_stride = p->q_batch_stride;
     kp.q_head_stride = p->q_head_stride;
     kp.o_batch_stride = p->o_batch_stride;
@@ -360,7 +405,7 @@ int mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_byte
     kp.seqlen_k = p->seqlen_k;
     kp.num_splits = splits;
     kp.head_tiles = (kp.group + mfa::kDecodeMaxGroup - 1) / mfa::kDecodeMaxGroup;
-    kp.partial_out = p->partial_out ? 1 : 0;
+    kp.partial_out = (p->partial_out || x) ? 1 : 0;
     kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);
     kp.scale_log2 = kp.scale * 1.4426950408889634f;
 
@@ -368,6 +413,34 @@ int mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_byte
     cudaError_t e = mfa::launch_decode(tmK, tmV, kp, bf16, dpad, stream);
     if (e != cudaSuccess) return cuda_fail(e, "decode launch");
     g_launches.fetch_add(1);
+    if (x) {
+        // local split merge + push over NVLink + wait + cross-rank merge: one kernel (xchg_sm100.cu)
+        mfa::XchgKParams xp{};
+        xp.o_part = static_cast<const float*>(workspace);
+        xp.lse_part = static_cast<const float*>(workspace) + (size_t)splits * rows * D;
+        for (int r = 0; r < x->world; ++r) {
+            xp.peer_data[r] = static_cast<float*>(x->peer[r]);
+            xp.peer_flags[r] = reinterpret_cast<uint32_t*>(static_cast<char*>(x->peer[r]) + x->data_bytes);
+        }
+        xp.status = reinterpret_cast<uint32_t*>(static_cast<char*>(x->local) + x->data_bytes + x->flag_bytes);
+        xp.out = p->o_ptr;
+        xp.lse_out = p->softmax_lse_ptr;
+        xp.out_batch_stride = p->o_batch_stride;
+        xp.out_head_stride = p->o_head_stride;
+        xp.timeout_cycles = x->timeout_cycles;
+        xp.num_splits = splits;
+        xp.world = x->world;
+        xp.rank = x->rank;
+        xp.rows = (int)rows;
+        xp.max_rows = x->max_rows;
+        xp.head_dim = D;
+        xp.heads = p->heads;
+        xp.epoch = ++x->epoch;
+        e = mfa::launch_xchg_merge(xp, bf16, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "exchange-merge launch");
+        g_launches.fetch_add(1);
+        return MFA_OK;
+    }
     if (splits > 1) {
         mfa::CombineKParams cp{};
         cp.out_f32 = p->partial_out ? 1 : 0;   // KV-sharded decode: the merged result stays a normalised fp32 partial
@@ -386,6 +459,110 @@ int mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_byte
         if (e != cudaSuccess) return cuda_fail(e, "combine launch");
         g_launches.fetch_add(1);
     }
+    return MFA_OK;
+}
+
+// ------------------------------------------------------------------------------------------ KV-shard exchange
+int mfa_xchg_create(int world, int rank, int max_rows, int head_dim, mfa_xchg_t** out) {
+    if (!out) return fail(MFA_ERR_INVALID_ARG, "null out");
+    if (world < 1 || world > MFA_XCHG_MAX_WORLD || rank < 0 || rank >= world)
+        return fail(MFA_ERR_INVALID_ARG, "world must be 1..%d and 0 <= rank < world (got %d, %d)", MFA_XCHG_MAX_WORLD, world, rank);
+    if (max_rows <= 0 || head_dim <= 0 || head_dim > 256 || head_dim % 8)
+        return fail(MFA_ERR_INVALID_ARG, "max_rows must be positive and head_dim a multiple of 8, <= 256");
+    int rc = check_device();
+    if (rc) return rc;
+    mfa_xchg_t* x = new mfa_xchg_t();
+    x->world = world;
+    x->rank = rank;
+    x->max_rows = max_rows;
+    x->head_dim = head_dim;
+    cudaGetDevice(&x->device);
+    x->data_bytes = (size_t)2 * world * max_rows * (head_dim + 4) * sizeof(float);
+    x->flag_bytes = (size_t)world * max_rows * sizeof(uint32_t);
+    x->bytes = x->data_bytes + x->flag_bytes + 16;
+    for (int r = 0; r < MFA_XCHG_MAX_WORLD; ++r) {
+        x->peer[r] = nullptr;
+        x->ipc_opened[r] = false;
+    }
+    x->connected = false;
+    x->epoch = 0;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, x->device);
+    x->timeout_cycles = (long long)(khz > 0 ? khz : 2000000) * 1000LL * 2LL;   // ~2 s of SM clocks
+    cudaError_t e = cudaMalloc(&x->local, x->bytes);
+    if (e != cudaSuccess) {
+        delete x;
+        return cuda_fail(e, "cudaMalloc(exchange buffer)");
+    }
+    e = cudaMemset(x->local, 0, x->bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        cudaFree(x->local);
+        delete x;
+        return cuda_fail(e, "cudaMemset(exchange buffer)");
+    }
+    x->peer[rank] = x->local;
+    if (world == 1) x->connected = true;
+    *out = x;
+    return MFA_OK;
+}
+
+int mfa_xchg_export(mfa_xchg_t* x, void* handle_out) {
+    if (!x || !handle_out) return fail(MFA_ERR_INVALID_ARG, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == MFA_XCHG_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, x->local);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaIpcGetMemHandle");
+    memcpy(handle_out, &h, sizeof(h));
+    return MFA_OK;
+}
+
+int mfa_xchg_connect(mfa_xchg_t* x, const void* handles) {
+    if (!x || !handles) return fail(MFA_ERR_INVALID_ARG, "null argument");
+    for (int r = 0; r < x->world; ++r) {
+        if (r == x->rank || x->peer[r]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const char*>(handles) + (size_t)r * MFA_XCHG_HANDLE_BYTES, sizeof(h));
+        void* ptr = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaIpcOpenMemHandle (peer access between the GPUs is required)");
+        x->peer[r] = ptr;
+        x->ipc_opened[r] = true;
+    }
+    x->connected = true;
+    return MFA_OK;
+}
+
+int mfa_xchg_connect_ptrs(mfa_xchg_t* x, void* const* peer_ptrs) {
+    if (!x || !peer_ptrs) return fail(MFA_ERR_INVALID_ARG, "null argument");
+    for (int r = 0; r < x->world; ++r) {
+        if (r == x->rank) continue;
+        if (!peer_ptrs[r]) return fail(MFA_ERR_INVALID_ARG, "null peer pointer for rank %d", r);
+        x->peer[r] = peer_ptrs[r];
+    }
+    x->connected = true;
+    return MFA_OK;
+}
+
+void* mfa_xchg_local_ptr(mfa_xchg_t* x) { return x ? x->local : nullptr; }
+
+int mfa_xchg_status(mfa_xchg_t* x) {
+    if (!x) return -1;
+    uint32_t st = 0;
+    cudaError_t e = cudaMemcpy(&st, static_cast<char*>(x->local) + x->data_bytes + x->flag_bytes, sizeof(st), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) {
+        cuda_fail(e, "exchange status read");
+        return -1;
+    }
+    return (int)st;
+}
+
+int mfa_xchg_destroy(mfa_xchg_t* x) {
+    if (!x) return MFA_OK;
+    for (int r = 0; r < x->world; ++r)
+        if (x->ipc_opened[r]) cudaIpcCloseMemHandle(x->peer[r]);
+    cudaFree(x->local);
+    delete x;
     return MFA_OK;
 }
 

@@ -44,6 +44,23 @@ struct CombineKParams {
     int32_t out_f32;           // write fp32 instead of the 16-bit dtype (partials of a KV-sharded decode)
 };
 
+constexpr int kXchgMaxWorld = 8;   // ranks of one NVSwitch domain
+
+// exchange + merge kernel of the KV-sharded decode (xchg_sm100.cu)
+struct XchgKParams {
+    const float* o_part;       // this rank's split partials (num_splits, rows, D) fp32, normalised
+    const float* lse_part;     // (num_splits, rows)
+    float* peer_data[kXchgMaxWorld];      // every rank's gather buffer [2 parities][world][max_rows][D + 4] (own included)
+    uint32_t* peer_flags[kXchgMaxWorld];  // every rank's flags [world][max_rows], epoch valued
+    uint32_t* status;          // local: != 0 after a wait timed out
+    void* out;                 // (batch, heads, D) out dtype through out_batch_stride / out_head_stride
+    float* lse_out;            // optional (rows)
+    int64_t out_batch_stride, out_head_stride;
+    long long timeout_cycles;
+    int32_t num_splits, world, rank, rows, max_rows, head_dim, heads;
+    uint32_t epoch;
+};
+
 constexpr int kPrefillBlockM = 128;   // query rows per Q tile (one TMEM lane per row)
 constexpr int kPrefillBlockN = 128;   // KV rows per tile
 constexpr int kPrefillThreads = 384;  // 2 softmax warpgroups + 1 warpgroup {TMA warp, MMA warp, 2 spare}

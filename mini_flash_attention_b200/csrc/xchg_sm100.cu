@@ -1,0 +1,184 @@
+// xchg_sm100.cu -- the exchange step of the KV-sharded (multi-GPU) decode, fused into the LSE-merge kernel.
+//
+// a long KV axis is cut over R GPUs; every rank computes a normalised partial (O_r, LSE_r) over its rows and
+// the final result is  LSE = logsumexp_r LSE_r,  O = sum_r exp(LSE_r - LSE) O_r  (the arithmetic of the reference's
+// combine kernel, /root/reference/csrc/mfa/decode.cuh:665-755, with a max-subtracted log-sum-exp).  The first form
+// of this path packs the partial, calls ONE NCCL all-gather and then the combine kernel; that costs ~0.25 ms of fixed
+// latency per step (profiles/multigpu_r01b.jsonl).  Here ONE kernel per rank does all of it over NVLink peer memory:
+//
+//   1. merge this rank's split-KV partials (S, rows, D) -> one normalised row + LSE        (registers)
+//   2. PUSH the row into slot [rank] of every peer's gather buffer (plain 16-byte stores through the peer mapping),
+//      fence.sys, then st.release.sys of the step's epoch into the peer's flag [rank][row]
+//   3. spin (ld.acquire.sys, bounded by a clock64() timeout) until the R flags of this row carry the epoch
+//   4. merge the R rows that the peers pushed into the LOCAL buffer, cast, store
+//
+// One warp owns one (batch, head) row end to end, flags are per (source rank, row), so there is no dependency between
+// warps or CTAs of a grid and no co-residency requirement; a rank never blocks another rank's push.  The gather buffer
+// is double-buffered by epoch parity: rank A can start step n+2 only after every peer pushed step n+1, i.e. after each
+// peer's step-n kernel finished (stream order), so the parity-n rows are no longer being read when A overwrites them.
+// Flags carry the monotonically increasing epoch and are never reset.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "kparams.h"
+
+namespace mfa {
+namespace {
+
+template <typename T>
+struct XPack;
+template <>
+struct XPack<__half> {
+    static __device__ __forceinline__ uint32_t pack(float a, float b) {
+        __half2 h = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+};
+template <>
+struct XPack<__nv_bfloat16> {
+    static __device__ __forceinline__ uint32_t pack(float a, float b) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// One warp per row; lanes own columns lane*4 + 128*i (head_dim <= 256 => at most 2 float4 per lane).
+template <typename T>
+__global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__ XchgKParams p) {
+    const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= p.rows) return;
+    const int D = p.head_dim;
+    const int DS = D + 4;   // row stride of the gather buffer: [O_0 .. O_{D-1}, LSE, pad x3] keeps rows 16-byte aligned
+
+    // ---- 1. local merge over this rank's splits (same arithmetic as combine_kernel)
+    float mx = -INFINITY;
+    for (int s = lane; s < p.num_splits; s += 32) mx = fmaxf(mx, p.lse_part[(int64_t)s * p.rows + row]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float tot = 0.f;
+    for (int s = lane; s < p.num_splits; s += 32) {
+        const float l = p.lse_part[(int64_t)s * p.rows + row];
+        tot += (l == -INFINITY) ? 0.f : __expf(l - mx);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    const float my_lse = (mx == -INFINITY) ? -INFINITY : mx + __logf(tot);
+    float4 mine[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+    for (int s = 0; s < p.num_splits; ++s) {
+        const float l = p.lse_part[(int64_t)s * p.rows + row];
+        if (l == -INFINITY) continue;
+        const float w = __expf(l - my_lse);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int col = lane * 4 + 128 * i;
+            if (col < D) {
+                const float4 v = *reinterpret_cast<const float4*>(p.o_part + ((int64_t)s * p.rows + row) * D + col);
+                mine[i].x += v.x * w;
+                mine[i].y += v.y * w;
+                mine[i].z += v.z * w;
+                mine[i].w += v.w * w;
+            }
+        }
+    }
+
+    // ---- 2. push to every rank's gather buffer (own included), then publish the epoch
+    const int parity = (int)(p.epoch & 1u);
+    const int64_t slot_off = (((int64_t)parity * p.world + p.rank) * p.max_rows + row) * DS;
+    for (int r = 0; r < p.world; ++r) {
+        float* dst = p.peer_data[r] + slot_off;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int col = lane * 4 + 128 * i;
+            if (col < D) *reinterpret_cast<float4*>(dst + col) = mine[i];
+        }
+        if (lane == 0) *reinterpret_cast<float4*>(dst + D) = make_float4(my_lse, 0.f, 0.f, 0.f);
+    }
+    __threadfence_system();
+    __syncwarp();
+    if (lane < p.world) {
+        __threadfence_system();
+        st_release_sys(p.peer_flags[lane] + (int64_t)p.rank * p.max_rows + row, p.epoch);
+    }
+
+    // ---- 3. wait for the R pushes of this row into the local buffer
+    if (lane < p.world) {
+        const uint32_t* f = p.peer_flags[p.rank] + (int64_t)lane * p.max_rows + row;
+        const long long t0 = clock64();
+        while ((int32_t)(ld_acquire_sys(f) - p.epoch) < 0) {
+            if (clock64() - t0 > p.timeout_cycles) {
+                atomicExch(p.status, 1u + (uint32_t)lane);   // a peer never arrived: reported by mfa_xchg_status()
+                break;
+            }
+            __nanosleep(64);
+        }
+    }
+    __syncwarp();
+    __threadfence_system();
+
+    // ---- 4. merge the R partial rows (L2 loads: the lines were written by peers, never trust L1)
+    const float* base = p.peer_data[p.rank] + ((int64_t)parity * p.world * p.max_rows + row) * DS;
+    const int64_t rstride = (int64_t)p.max_rows * DS;
+    float gmx = -INFINITY;
+    for (int r = 0; r < p.world; ++r) gmx = fmaxf(gmx, __ldcg(base + r * rstride + D));
+    float gtot = 0.f;
+    for (int r = 0; r < p.world; ++r) {
+        const float l = __ldcg(base + r * rstride + D);
+        gtot += (l == -INFINITY) ? 0.f : __expf(l - gmx);
+    }
+    const float glse = (gmx == -INFINITY) ? -INFINITY : gmx + __logf(gtot);
+    float4 acc[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+    for (int r = 0; r < p.world; ++r) {
+        const float l = __ldcg(base + r * rstride + D);
+        if (l == -INFINITY) continue;
+        const float w = __expf(l - glse);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int col = lane * 4 + 128 * i;
+            if (col < D) {
+                const float4 v = __ldcg(reinterpret_cast<const float4*>(base + r * rstride + col));
+                acc[i].x += v.x * w;
+                acc[i].y += v.y * w;
+                acc[i].z += v.z * w;
+                acc[i].w += v.w * w;
+            }
+        }
+    }
+    T* out = static_cast<T*>(p.out) + (int64_t)(row / p.heads) * p.out_batch_stride + (int64_t)(row % p.heads) * p.out_head_stride;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int col = lane * 4 + 128 * i;
+        if (col < D) {
+            uint2 pk;
+            pk.x = XPack<T>::pack(acc[i].x, acc[i].y);
+            pk.y = XPack<T>::pack(acc[i].z, acc[i].w);
+            *reinterpret_cast<uint2*>(out + col) = pk;
+        }
+    }
+    if (lane == 0 && p.lse_out) p.lse_out[row] = glse;
+}
+
+}  // namespace
+
+cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream) {
+    dim3 grid((p.rows + 3) / 4);
+    if (is_bf16)
+        xchg_merge_kernel<__nv_bfloat16><<<grid, 128, 0, stream>>>(p);
+    else
+        xchg_merge_kernel<__half><<<grid, 128, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace mfa

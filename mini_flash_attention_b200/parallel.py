@@ -145,15 +145,79 @@ def pack_partial(o_part: torch.Tensor, lse_part: torch.Tensor) -> torch.Tensor:
     return packed
 
 
+class KVShardExchange:
+    """Peer-memory exchange buffers of the KV-sharded decode (include/mfa_b200.h `mfa_xchg_*`): one gather buffer per
+    rank, mapped into every peer with CUDA IPC, so that the merge kernel of `decode_kv_sharded(..., exchange=x)` pushes
+    its partial row straight into the peers' memory over NVLink instead of going through an NCCL all-gather.
+
+    One process per GPU: `KVShardExchange(world, rank, max_rows, head_dim, group=g)` allocates the local buffer on the
+    current device, all-gathers the 64-byte IPC handles over `group` (torch.distributed, any backend) and opens the
+    peers.  Collective: every rank of the group must construct it, and later call decode_kv_sharded the same number of
+    times in the same order.  `KVShardExchange.local_group(world, ...)` builds all ranks inside ONE process on one
+    device (tests: the ranks' kernels then run on different streams of the same GPU)."""
+
+    def __init__(self, world: int, rank: int, max_rows: int, head_dim: int, group=None, _connect: bool = True):
+        import ctypes
+        from . import _lib
+        self._lib = _lib.load()
+        self.world, self.rank, self.max_rows, self.head_dim = world, rank, max_rows, head_dim
+        h = ctypes.c_void_p()
+        _lib.check(self._lib.mfa_xchg_create(world, rank, max_rows, head_dim, ctypes.byref(h)), "mfa_xchg_create")
+        self.handle = h.value
+        if _connect and world > 1:
+            import torch.distributed as dist
+            mine = ctypes.create_string_buffer(_lib.XCHG_HANDLE_BYTES)
+            _lib.check(self._lib.mfa_xchg_export(self.handle, mine), "mfa_xchg_export")
+            handles = [None] * world
+            dist.all_gather_object(handles, bytes(mine.raw), group=group)
+            blob = ctypes.create_string_buffer(b"".join(handles), world * _lib.XCHG_HANDLE_BYTES)
+            _lib.check(self._lib.mfa_xchg_connect(self.handle, blob), "mfa_xchg_connect")
+            dist.barrier(group=group)   # every rank has mapped every buffer before the first push
+
+    @classmethod
+    def local_group(cls, world: int, max_rows: int, head_dim: int):
+        import ctypes
+        from . import _lib
+        xs = [cls(world, r, max_rows, head_dim, _connect=False) for r in range(world)]
+        ptrs = (ctypes.c_void_p * world)(*[x._lib.mfa_xchg_local_ptr(x.handle) for x in xs])
+        for x in xs:
+            if world > 1:
+                _lib.check(x._lib.mfa_xchg_connect_ptrs(x.handle, ptrs), "mfa_xchg_connect_ptrs")
+        return xs
+
+    def status(self) -> int:
+        """0, or 1 + the rank whose push did not arrive within the kernel's ~2 s timeout (synchronises the device)."""
+        return int(self._lib.mfa_xchg_status(self.handle))
+
+    def close(self) -> None:
+        if getattr(self, "handle", None):
+            self._lib.mfa_xchg_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def decode_kv_sharded(q: torch.Tensor, k_cache_local: torch.Tensor, v_cache_local: torch.Tensor,
                       local_seqlens: torch.Tensor, block_table_local: Optional[torch.Tensor] = None, *,
                       world: int, group=None, num_splits: int = 0, partial_fn: Optional[Callable] = None,
-                      combine_fn: Optional[Callable] = None, gathered: Optional[torch.Tensor] = None) -> torch.Tensor:
+                      combine_fn: Optional[Callable] = None, gathered: Optional[torch.Tensor] = None,
+                      exchange: Optional[KVShardExchange] = None) -> torch.Tensor:
     """flash_attn_with_kvcache with the KV axis sharded over `world` ranks.
 
     q (B,1,Hq,D) is replicated; k_cache_local / v_cache_local / block_table_local / local_seqlens describe only
     THIS rank's rows of every sequence (see kv_shard_lengths / kv_shard_block_table).  Returns the full result
-    (B,1,Hq,D) in q's dtype on every rank.  One all-gather of B*Hq*(D+1) floats per rank."""
+    (B,1,Hq,D) in q's dtype on every rank.  One all-gather of B*Hq*(D+1) floats per rank -- or, with
+    `exchange` (a KVShardExchange), no collective at all: the merge kernel pushes the rows over NVLink peer memory."""
+    if exchange is not None:
+        from . import _C
+        if exchange.world != world:
+            raise ValueError("exchange was built for another world size")
+        return _C.decode_kv_sharded_fused(q, k_cache_local, v_cache_local, local_seqlens, block_table_local, num_splits,
+                                          exchange.handle)
     if partial_fn is None or combine_fn is None:
         from . import _C
         partial_fn = partial_fn or _C.decode_partial
