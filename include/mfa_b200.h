@@ -168,6 +168,8 @@ int mfa_combine_partials(const float* packed, int num_partials, int rows, int he
  *     merges the local splits, pushes the normalised row + LSE into every peer's gather buffer (P2P stores + release
  *     flag), waits for the peers' rows and writes the final output (p->o_ptr, out dtype; optional p->softmax_lse_ptr):
  *     no NCCL call, no host synchronisation.  All ranks must call it the same number of times, in the same order.
+ *     The step counter (epoch) lives in device memory, so the launches are identical from step to step and the call
+ *     can be captured in a CUDA graph and replayed.
  *   mfa_xchg_create:  allocates this rank's gather buffer (cudaMalloc on the current device), max_rows >= batch*heads
  *   mfa_xchg_export:  writes the MFA_XCHG_HANDLE_BYTES-byte IPC handle of that buffer (exchange it out of band, e.g.
  *                     with torch.distributed.all_gather_object)

@@ -31,7 +31,7 @@ cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t s
 }  // namespace mfa
 
 // Exchange buffer of the KV-sharded decode (include/mfa_b200.h; kernel in xchg_sm100.cu).  One cudaMalloc per rank:
-//   floats [2 parities][world][max_rows][head_dim + 4]  |  uint32 flags [world][max_rows]  |  uint32 status[4]
+//   floats [2 parities][world][max_rows][head_dim + 4]  |  uint32 flags [world][max_rows]  |  uint32 {status, epoch, done, pad}
 struct mfa_xchg {
     int world, rank, max_rows, head_dim, device;
     size_t data_bytes, flag_bytes, bytes;
@@ -39,7 +39,6 @@ struct mfa_xchg {
     void* peer[MFA_XCHG_MAX_WORLD];
     bool ipc_opened[MFA_XCHG_MAX_WORLD];
     bool connected;
-    uint32_t epoch;
     long long timeout_cycles;
 };
 
@@ -422,7 +421,7 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
             xp.peer_data[r] = static_cast<float*>(x->peer[r]);
             xp.peer_flags[r] = reinterpret_cast<uint32_t*>(static_cast<char*>(x->peer[r]) + x->data_bytes);
         }
-        xp.status = reinterpret_cast<uint32_t*>(static_cast<char*>(x->local) + x->data_bytes + x->flag_bytes);
+        xp.ctrs = reinterpret_cast<uint32_t*>(static_cast<char*>(x->local) + x->data_bytes + x->flag_bytes);
         xp.out = p->o_ptr;
         xp.lse_out = p->softmax_lse_ptr;
         xp.out_batch_stride = p->o_batch_stride;
@@ -435,7 +434,6 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
         xp.max_rows = x->max_rows;
         xp.head_dim = D;
         xp.heads = p->heads;
-        xp.epoch = ++x->epoch;
         e = mfa::launch_xchg_merge(xp, bf16, stream);
         if (e != cudaSuccess) return cuda_fail(e, "exchange-merge launch");
         g_launches.fetch_add(1);
@@ -485,7 +483,6 @@ int mfa_xchg_create(int world, int rank, int max_rows, int head_dim, mfa_xchg_t*
         x->ipc_opened[r] = false;
     }
     x->connected = false;
-    x->epoch = 0;
     int khz = 0;
     cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, x->device);
     x->timeout_cycles = (long long)(khz > 0 ? khz : 2000000) * 1000LL * 2LL;   // ~2 s of SM clocks

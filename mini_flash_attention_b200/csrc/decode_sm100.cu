@@ -414,31 +414,52 @@ __global__ void __launch_bounds__(128) combine_kernel(const __grid_constant__ Co
                                           : (int64_t)row * p.out_row_stride;
     T* out = static_cast<T*>(p.out) + out_off;
     float* out32 = static_cast<float*>(p.out) + out_off;
-    for (int col = lane * 4; col < D; col += 128) {
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int s = 0; s < p.num_splits; ++s) {
-            const float l = lse_of(s);
-            if (l == -INFINITY) continue;
-            const float w = __expf(l - glse);
-            const float* src = p.o_part + ((int64_t)s * p.rows + row) * pstride + col;
-            float4 v;
-            if (p.packed) {   // rows of D+1 floats are not 16-byte aligned
-                v = make_float4(src[0], src[1], src[2], src[3]);
-            } else {
-                v = *reinterpret_cast<const float4*>(src);
+    // Weights once per chunk of 32 splits (lane s holds the weight of split base + s, broadcast by shuffle), so that the
+    // loop over splits has no dependent scalar load in front of every row load and the row loads of several splits
+    // are in flight together.  (The first form loaded lse(s) and then the row, split after split: ~1.3 us per split,
+    // 45 us of the 85 us of a 37-split long-context step.)
+    float4 acc[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+    for (int base = 0; base < p.num_splits; base += 32) {
+        const int s_mine = base + lane;
+        const float l_mine = (s_mine < p.num_splits) ? lse_of(s_mine) : -INFINITY;
+        const float w_mine = (l_mine == -INFINITY) ? 0.f : __expf(l_mine - glse);
+        const int n = min(32, p.num_splits - base);
+#pragma unroll 4
+        for (int j = 0; j < n; ++j) {
+            const float w = __shfl_sync(0xffffffffu, w_mine, j);
+            const float* src = p.o_part + ((int64_t)(base + j) * p.rows + row) * pstride;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int col = lane * 4 + 128 * i;
+                if (col < D) {
+                    float4 v;
+                    if (p.packed) {   // rows of D+1 floats are not 16-byte aligned
+                        v = make_float4(src[col], src[col + 1], src[col + 2], src[col + 3]);
+                    } else {
+                        v = *reinterpret_cast<const float4*>(src + col);
+                    }
+                    if (w != 0.f) {
+                        acc[i].x += v.x * w;
+                        acc[i].y += v.y * w;
+                        acc[i].z += v.z * w;
+                        acc[i].w += v.w * w;
+                    }
+                }
             }
-            acc.x += v.x * w;
-            acc.y += v.y * w;
-            acc.z += v.z * w;
-            acc.w += v.w * w;
         }
-        if (p.out_f32) {
-            *reinterpret_cast<float4*>(out32 + col) = acc;
-        } else {
-            uint2 pk;
-            pk.x = Pack2<T>::pack(acc.x, acc.y);
-            pk.y = Pack2<T>::pack(acc.z, acc.w);
-            *reinterpret_cast<uint2*>(out + col) = pk;
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int col = lane * 4 + 128 * i;
+        if (col < D) {
+            if (p.out_f32) {
+                *reinterpret_cast<float4*>(out32 + col) = acc[i];
+            } else {
+                uint2 pk;
+                pk.x = Pack2<T>::pack(acc[i].x, acc[i].y);
+                pk.y = Pack2<T>::pack(acc[i].z, acc[i].w);
+                *reinterpret_cast<uint2*>(out + col) = pk;
+            }
         }
     }
     if (lane == 0 && p.lse_out) p.lse_out[row] = glse;

@@ -52,13 +52,12 @@ struct XchgKParams {
     const float* lse_part;     // (num_splits, rows)
     float* peer_data[kXchgMaxWorld];      // every rank's gather buffer [2 parities][world][max_rows][D + 4] (own included)
     uint32_t* peer_flags[kXchgMaxWorld];  // every rank's flags [world][max_rows], epoch valued
-    uint32_t* status;          // local: != 0 after a wait timed out
+    uint32_t* ctrs;            // local {status (!= 0 after a wait timed out), epoch counter, warps done, pad}
     void* out;                 // (batch, heads, D) out dtype through out_batch_stride / out_head_stride
     float* lse_out;            // optional (rows)
     int64_t out_batch_stride, out_head_stride;
     long long timeout_cycles;
     int32_t num_splits, world, rank, rows, max_rows, head_dim, heads;
-    uint32_t epoch;
 };
 
 constexpr int kPrefillBlockM = 128;   // query rows per Q tile (one TMEM lane per row)

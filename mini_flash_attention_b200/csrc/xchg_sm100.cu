@@ -16,7 +16,9 @@
 // warps or CTAs of a grid and no co-residency requirement; a rank never blocks another rank's push.  The gather buffer
 // is double-buffered by epoch parity: rank A can start step n+2 only after every peer pushed step n+1, i.e. after each
 // peer's step-n kernel finished (stream order), so the parity-n rows are no longer being read when A overwrites them.
-// Flags carry the monotonically increasing epoch and are never reset.
+// Flags carry the monotonically increasing epoch and are never reset.  The epoch itself lives in DEVICE memory (ctrs[1]):
+// every warp reads it on entry, and the last warp of the grid to finish bumps it for the next launch, so the launch
+// parameters do not change from step to step and the whole step can be captured in a CUDA graph and replayed.
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -62,6 +64,8 @@ __global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__
     if (row >= p.rows) return;
     const int D = p.head_dim;
     const int DS = D + 4;   // row stride of the gather buffer: [O_0 .. O_{D-1}, LSE, pad x3] keeps rows 16-byte aligned
+    // this step's epoch: launches completed so far + 1 (ctrs = {status, epoch counter, warps done})
+    const uint32_t epoch = *reinterpret_cast<volatile const uint32_t*>(p.ctrs + 1) + 1u;
 
     // ---- 1. local merge over this rank's splits (same arithmetic as combine_kernel)
     float mx = -INFINITY;
@@ -76,26 +80,35 @@ __global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
     const float my_lse = (mx == -INFINITY) ? -INFINITY : mx + __logf(tot);
+    // (weights per chunk of 32 splits in lanes, broadcast by shuffle: no dependent scalar load in front of each row load)
     float4 mine[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
-    for (int s = 0; s < p.num_splits; ++s) {
-        const float l = p.lse_part[(int64_t)s * p.rows + row];
-        if (l == -INFINITY) continue;
-        const float w = __expf(l - my_lse);
+    for (int base = 0; base < p.num_splits; base += 32) {
+        const int s_mine = base + lane;
+        const float l_mine = (s_mine < p.num_splits) ? p.lse_part[(int64_t)s_mine * p.rows + row] : -INFINITY;
+        const float w_mine = (l_mine == -INFINITY) ? 0.f : __expf(l_mine - my_lse);
+        const int n = min(32, p.num_splits - base);
+#pragma unroll 4
+        for (int j = 0; j < n; ++j) {
+            const float w = __shfl_sync(0xffffffffu, w_mine, j);
+            const float* src = p.o_part + ((int64_t)(base + j) * p.rows + row) * D;
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const int col = lane * 4 + 128 * i;
-            if (col < D) {
-                const float4 v = *reinterpret_cast<const float4*>(p.o_part + ((int64_t)s * p.rows + row) * D + col);
-                mine[i].x += v.x * w;
-                mine[i].y += v.y * w;
-                mine[i].z += v.z * w;
-                mine[i].w += v.w * w;
+            for (int i = 0; i < 2; ++i) {
+                const int col = lane * 4 + 128 * i;
+                if (col < D) {
+                    const float4 v = *reinterpret_cast<const float4*>(src + col);
+                    if (w != 0.f) {
+                        mine[i].x += v.x * w;
+                        mine[i].y += v.y * w;
+                        mine[i].z += v.z * w;
+                        mine[i].w += v.w * w;
+                    }
+                }
             }
         }
     }
 
     // ---- 2. push to every rank's gather buffer (own included), then publish the epoch
-    const int parity = (int)(p.epoch & 1u);
+    const int parity = (int)(epoch & 1u);
     const int64_t slot_off = (((int64_t)parity * p.world + p.rank) * p.max_rows + row) * DS;
     for (int r = 0; r < p.world; ++r) {
         float* dst = p.peer_data[r] + slot_off;
@@ -110,16 +123,16 @@ __global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__
     __syncwarp();
     if (lane < p.world) {
         __threadfence_system();
-        st_release_sys(p.peer_flags[lane] + (int64_t)p.rank * p.max_rows + row, p.epoch);
+        st_release_sys(p.peer_flags[lane] + (int64_t)p.rank * p.max_rows + row, epoch);
     }
 
     // ---- 3. wait for the R pushes of this row into the local buffer
     if (lane < p.world) {
         const uint32_t* f = p.peer_flags[p.rank] + (int64_t)lane * p.max_rows + row;
         const long long t0 = clock64();
-        while ((int32_t)(ld_acquire_sys(f) - p.epoch) < 0) {
+        while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
             if (clock64() - t0 > p.timeout_cycles) {
-                atomicExch(p.status, 1u + (uint32_t)lane);   // a peer never arrived: reported by mfa_xchg_status()
+                atomicExch(p.ctrs, 1u + (uint32_t)lane);   // a peer never arrived: reported by mfa_xchg_status()
                 break;
             }
             __nanosleep(64);
@@ -131,28 +144,30 @@ __global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__
     // ---- 4. merge the R partial rows (L2 loads: the lines were written by peers, never trust L1)
     const float* base = p.peer_data[p.rank] + ((int64_t)parity * p.world * p.max_rows + row) * DS;
     const int64_t rstride = (int64_t)p.max_rows * DS;
-    float gmx = -INFINITY;
-    for (int r = 0; r < p.world; ++r) gmx = fmaxf(gmx, __ldcg(base + r * rstride + D));
-    float gtot = 0.f;
-    for (int r = 0; r < p.world; ++r) {
-        const float l = __ldcg(base + r * rstride + D);
-        gtot += (l == -INFINITY) ? 0.f : __expf(l - gmx);
-    }
+    const float l_r = (lane < p.world) ? __ldcg(base + lane * rstride + D) : -INFINITY;   // lane r: rank r's LSE
+    float gmx = l_r;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) gmx = fmaxf(gmx, __shfl_xor_sync(0xffffffffu, gmx, o));
+    float gtot = (l_r == -INFINITY) ? 0.f : __expf(l_r - gmx);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) gtot += __shfl_xor_sync(0xffffffffu, gtot, o);
     const float glse = (gmx == -INFINITY) ? -INFINITY : gmx + __logf(gtot);
+    const float w_r = (l_r == -INFINITY) ? 0.f : __expf(l_r - glse);
     float4 acc[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+#pragma unroll 4
     for (int r = 0; r < p.world; ++r) {
-        const float l = __ldcg(base + r * rstride + D);
-        if (l == -INFINITY) continue;
-        const float w = __expf(l - glse);
+        const float w = __shfl_sync(0xffffffffu, w_r, r);
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             const int col = lane * 4 + 128 * i;
             if (col < D) {
                 const float4 v = __ldcg(reinterpret_cast<const float4*>(base + r * rstride + col));
-                acc[i].x += v.x * w;
-                acc[i].y += v.y * w;
-                acc[i].z += v.z * w;
-                acc[i].w += v.w * w;
+                if (w != 0.f) {
+                    acc[i].x += v.x * w;
+                    acc[i].y += v.y * w;
+                    acc[i].z += v.z * w;
+                    acc[i].w += v.w * w;
+                }
             }
         }
     }
@@ -168,6 +183,17 @@ __global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__
         }
     }
     if (lane == 0 && p.lse_out) p.lse_out[row] = glse;
+
+    // ---- 5. the last warp of the grid closes the step: every warp has read the epoch before it got here
+    __syncwarp();
+    if (lane == 0) {
+        __threadfence();
+        if (atomicAdd(p.ctrs + 2, 1u) == (uint32_t)p.rows - 1u) {
+            p.ctrs[2] = 0u;
+            __threadfence();
+            atomicAdd(p.ctrs + 1, 1u);
+        }
+    }
 }
 
 }  // namespace

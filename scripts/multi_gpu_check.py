@@ -4,8 +4,9 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
         scripts/multi_gpu_check.py [--quick]
 
-1. parity: KV-sharded decode (partial O + LSE per rank -> ONE all_gather -> combine kernel) against the fp32
-   oracle on the full, unsharded problem (paged cache, ragged lengths, GQA);
+1. parity: KV-sharded decode against the fp32 oracle on the full, unsharded problem (paged cache, ragged lengths,
+   GQA), both forms: partial O + LSE per rank -> ONE all_gather -> combine kernel, and the exchange fused into the
+   merge kernel over NVLink peer memory (KVShardExchange: no NCCL call on the data path);
 2. parity: prefill sharded by (batch, kv-head) with no collective, every rank's shard against the oracle;
 3. timing (device events, max over ranks): long-context decode KV = 128K ... 1M rows split over the ranks,
    B=1, Hq=32, Hkv=8, D=128, and head-sharded prefill S=16K.
@@ -52,6 +53,28 @@ def timed(fn, steps, warmup, world):
     return float(t.item())
 
 
+def latency(fn, steps, warmup, world):
+    """One ISOLATED step at a time (ranks aligned by a barrier + device sync before each): launch-to-completion time of
+    a single decode step, median over `steps`, max over ranks -- what a serving loop that needs the token waits for."""
+    ts = []
+    for i in range(warmup + steps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= warmup:
+            ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    t = torch.tensor([ts[len(ts) // 2]], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
@@ -88,6 +111,23 @@ def main():
     emit(rank, {"check": "decode_kv_sharded parity", "world": world, "max_abs_err": float(err), "tol": tol,
                 "ok": bool(float(err) <= tol)})
     assert float(err) <= tol, float(err)
+    # the same through the fused exchange (CUDA IPC peer buffers, push + flag + merge in one kernel)
+    xchg = P.KVShardExchange(world, rank, B * Hq, D)
+    sl_r, bt_r = P.kv_shard_lengths(lens, rank, rows), P.kv_shard_block_table(bt, rank, rows, page)
+    for step in range(3):
+        out_f = P.decode_kv_sharded(q, kc, vc, sl_r, bt_r, world=world, exchange=xchg)
+    st = torch.tensor([float(xchg.status())], device="cuda")
+    ferr = (out_f.float() - ref).abs().max()
+    same = (out_f.float() - out.float()).abs().max()
+    if world > 1:
+        dist.all_reduce(ferr, op=dist.ReduceOp.MAX)
+        dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        dist.all_reduce(same, op=dist.ReduceOp.MAX)
+    emit(rank, {"check": "decode_kv_sharded FUSED exchange parity", "world": world, "max_abs_err": float(ferr), "tol": tol,
+                "vs_allgather_path": float(same), "timeout_status": int(st.item()),
+                "ok": bool(float(ferr) <= tol and int(st.item()) == 0)})
+    assert float(ferr) <= tol and int(st.item()) == 0, (float(ferr), int(st.item()))
+    xchg.close()
 
     # ------------------------------------------------------------------ 2. sharded prefill parity
     Bp, Sp, Hp, Hkp = 2, 384, 8, 2
@@ -126,6 +166,42 @@ def main():
         emit(rank, {"bench": "long-context decode, KV axis sharded", "world": world, "kv": KV, "B": Bl, "Hq": Hq, "Hkv": Hkv,
                     "ms": round(ms, 4), "aggregate_GBps": round(nbytes / ms / 1e6, 1),
                     "per_gpu_GBps": round(nbytes / ms / 1e6 / world, 1), "collective": "1 all_gather of B*Hq*(D+1) fp32 per rank"})
+        xl = P.KVShardExchange(world, rank, Bl * Hq, D)
+        fn2 = lambda: P.decode_kv_sharded(ql, kl, vl, ll, btl, world=world, exchange=xl)  # noqa: E731
+        ms2 = timed(fn2, 30, 5, world)
+        lat_ag = latency(fn, 20, 3, world)
+        lat_fused = latency(fn2, 20, 3, world)
+        # the fused step has launch parameters that never change (the epoch lives on the device): capture + replay
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                fn2()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out_g = fn2()
+        ms3 = timed(graph.replay, 30, 5, world)
+        lat_graph = latency(graph.replay, 20, 3, world)
+        ref_out = fn()
+        torch.cuda.synchronize()
+        gerr = (out_g.float() - ref_out.float()).abs().max()
+        if world > 1:
+            dist.all_reduce(gerr, op=dist.ReduceOp.MAX)
+        st = xl.status()
+        emit(rank, {"bench": "long-context decode, KV axis sharded, FUSED exchange", "world": world, "kv": KV, "B": Bl, "Hq": Hq,
+                    "Hkv": Hkv, "ms": round(ms2, 4), "ms_graph_replay": round(ms3, 4),
+                    "aggregate_GBps": round(nbytes / ms2 / 1e6, 1), "aggregate_GBps_graph": round(nbytes / ms3 / 1e6, 1),
+                    "per_gpu_GBps_graph": round(nbytes / ms3 / 1e6 / world, 1),
+                    "step_latency_ms": {"allgather_path": round(lat_ag, 4), "fused": round(lat_fused, 4),
+                                        "fused_graph": round(lat_graph, 4)},
+                    "graph_vs_allgather_max_abs_diff": float(gerr), "timeout_status": st,
+                    "collective": "none: P2P push + flag inside the merge kernel (NVLink peer memory)"})
+        del graph, out_g
+        xl.close()
         del kl, vl
         torch.cuda.empty_cache()
     # head-sharded prefill S=16K (B=1, H=32, Hkv=8): strong scaling, no collective
