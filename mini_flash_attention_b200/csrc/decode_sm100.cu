@@ -19,6 +19,7 @@
 #include <cuda_fp16.h>
 
 #include "kparams.h"
+#include "merge.cuh"
 #include "ptx.cuh"
 
 namespace mfa {
@@ -384,70 +385,22 @@ __global__ void __launch_bounds__(kDecodeThreads) decode_splitkv_kernel(const __
 
 // LSE merge of `num_splits` normalised partials (decode.cuh:665-755 restated with a max-subtracted
 // log-sum-exp and no shared memory proportional to the split count).
-// One warp per output row (b, h); lanes stride over head_dim in float4.
-template <typename T>
-__global__ void __launch_bounds__(128) combine_kernel(const __grid_constant__ CombineKParams p) {
-    const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+// One CTA of 8 warps per output row (b, h): the splits are dealt over the warps (merge.cuh), warp 0 stores.
+template <typename T, bool kPacked>
+__global__ void __launch_bounds__(kMergeThreads) combine_kernel(const __grid_constant__ CombineKParams p) {
+    __shared__ __align__(16) float red[kMergeWarps * 256];
+    const int row = blockIdx.x;
     const int lane = threadIdx.x & 31;
-    if (row >= p.rows) return;
     const int D = p.head_dim;
-    const int pstride = p.packed ? (D + 1) : D;
-    auto lse_of = [&](int s) -> float {
-        return p.packed ? p.o_part[((int64_t)s * p.rows + row) * pstride + D]
-                        : p.lse_part[(int64_t)s * p.rows + row];
-    };
-    float mx = -INFINITY;
-    for (int s = lane; s < p.num_splits; s += 32) mx = fmaxf(mx, lse_of(s));
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    float tot = 0.f;
-    for (int s = lane; s < p.num_splits; s += 32) {
-        const float l = lse_of(s);
-        tot += (l == -INFINITY) ? 0.f : __expf(l - mx);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-    const float glse = (mx == -INFINITY) ? -INFINITY : mx + __logf(tot);
-
+    float4 acc[2];
+    float glse;
+    block_merge_splits<kPacked>(p.o_part, p.lse_part, p.num_splits, p.rows, row, D, acc, glse, red);
+    if (threadIdx.x >= 32) return;
     const int64_t out_off = (p.heads > 0) ? (int64_t)(row / p.heads) * p.out_batch_stride +
                                                 (int64_t)(row % p.heads) * p.out_head_stride
                                           : (int64_t)row * p.out_row_stride;
     T* out = static_cast<T*>(p.out) + out_off;
     float* out32 = static_cast<float*>(p.out) + out_off;
-    // Weights once per chunk of 32 splits (lane s holds the weight of split base + s, broadcast by shuffle), so that the
-    // loop over splits has no dependent scalar load in front of every row load and the row loads of several splits
-    // are in flight together.  (The first form loaded lse(s) and then the row, split after split: ~1.3 us per split,
-    // 45 us of the 85 us of a 37-split long-context step.)
-    float4 acc[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
-    for (int base = 0; base < p.num_splits; base += 32) {
-        const int s_mine = base + lane;
-        const float l_mine = (s_mine < p.num_splits) ? lse_of(s_mine) : -INFINITY;
-        const float w_mine = (l_mine == -INFINITY) ? 0.f : __expf(l_mine - glse);
-        const int n = min(32, p.num_splits - base);
-#pragma unroll 4
-        for (int j = 0; j < n; ++j) {
-            const float w = __shfl_sync(0xffffffffu, w_mine, j);
-            const float* src = p.o_part + ((int64_t)(base + j) * p.rows + row) * pstride;
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                const int col = lane * 4 + 128 * i;
-                if (col < D) {
-                    float4 v;
-                    if (p.packed) {   // rows of D+1 floats are not 16-byte aligned
-                        v = make_float4(src[col], src[col + 1], src[col + 2], src[col + 3]);
-                    } else {
-                        v = *reinterpret_cast<const float4*>(src + col);
-                    }
-                    if (w != 0.f) {
-                        acc[i].x += v.x * w;
-                        acc[i].y += v.y * w;
-                        acc[i].z += v.z * w;
-                        acc[i].w += v.w * w;
-                    }
-                }
-            }
-        }
-    }
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
         const int col = lane * 4 + 128 * i;
@@ -503,11 +456,18 @@ cudaError_t launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const 
 }
 
 cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream) {
-    dim3 grid((p.rows + 3) / 4);
-    if (is_bf16)
-        combine_kernel<__nv_bfloat16><<<grid, 128, 0, stream>>>(p);
-    else
-        combine_kernel<__half><<<grid, 128, 0, stream>>>(p);
+    dim3 grid(p.rows);
+    if (p.packed) {
+        if (is_bf16)
+            combine_kernel<__nv_bfloat16, true><<<grid, kMergeThreads, 0, stream>>>(p);
+        else
+            combine_kernel<__half, true><<<grid, kMergeThreads, 0, stream>>>(p);
+    } else {
+        if (is_bf16)
+            combine_kernel<__nv_bfloat16, false><<<grid, kMergeThreads, 0, stream>>>(p);
+        else
+            combine_kernel<__half, false><<<grid, kMergeThreads, 0, stream>>>(p);
+    }
     return cudaGetLastError();
 }
 

@@ -26,6 +26,7 @@
 #include <cstdint>
 
 #include "kparams.h"
+#include "merge.cuh"
 
 namespace mfa {
 namespace {
@@ -56,56 +57,23 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     return v;
 }
 
-// One warp per row; lanes own columns lane*4 + 128*i (head_dim <= 256 => at most 2 float4 per lane).
+// One CTA of 8 warps per row: the local splits are dealt over the warps (merge.cuh); warp 0 then owns the row -- push,
+// flag, wait, cross-rank merge, store.  Lanes own columns lane*4 + 128*i (head_dim <= 256 => at most 2 float4 per lane).
 template <typename T>
-__global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__ XchgKParams p) {
-    const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+__global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_constant__ XchgKParams p) {
+    __shared__ __align__(16) float red[kMergeWarps * 256];
+    const int row = blockIdx.x;
     const int lane = threadIdx.x & 31;
-    if (row >= p.rows) return;
     const int D = p.head_dim;
     const int DS = D + 4;   // row stride of the gather buffer: [O_0 .. O_{D-1}, LSE, pad x3] keeps rows 16-byte aligned
-    // this step's epoch: launches completed so far + 1 (ctrs = {status, epoch counter, warps done})
+    // this step's epoch: launches completed so far + 1 (ctrs = {status, epoch counter, rows done})
     const uint32_t epoch = *reinterpret_cast<volatile const uint32_t*>(p.ctrs + 1) + 1u;
 
-    // ---- 1. local merge over this rank's splits (same arithmetic as combine_kernel)
-    float mx = -INFINITY;
-    for (int s = lane; s < p.num_splits; s += 32) mx = fmaxf(mx, p.lse_part[(int64_t)s * p.rows + row]);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    float tot = 0.f;
-    for (int s = lane; s < p.num_splits; s += 32) {
-        const float l = p.lse_part[(int64_t)s * p.rows + row];
-        tot += (l == -INFINITY) ? 0.f : __expf(l - mx);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-    const float my_lse = (mx == -INFINITY) ? -INFINITY : mx + __logf(tot);
-    // (weights per chunk of 32 splits in lanes, broadcast by shuffle: no dependent scalar load in front of each row load)
-    float4 mine[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
-    for (int base = 0; base < p.num_splits; base += 32) {
-        const int s_mine = base + lane;
-        const float l_mine = (s_mine < p.num_splits) ? p.lse_part[(int64_t)s_mine * p.rows + row] : -INFINITY;
-        const float w_mine = (l_mine == -INFINITY) ? 0.f : __expf(l_mine - my_lse);
-        const int n = min(32, p.num_splits - base);
-#pragma unroll 4
-        for (int j = 0; j < n; ++j) {
-            const float w = __shfl_sync(0xffffffffu, w_mine, j);
-            const float* src = p.o_part + ((int64_t)(base + j) * p.rows + row) * D;
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                const int col = lane * 4 + 128 * i;
-                if (col < D) {
-                    const float4 v = *reinterpret_cast<const float4*>(src + col);
-                    if (w != 0.f) {
-                        mine[i].x += v.x * w;
-                        mine[i].y += v.y * w;
-                        mine[i].z += v.z * w;
-                        mine[i].w += v.w * w;
-                    }
-                }
-            }
-        }
-    }
+    // ---- 1. local merge over this rank's splits
+    float4 mine[2];
+    float my_lse;
+    block_merge_splits<false>(p.o_part, p.lse_part, p.num_splits, p.rows, row, D, mine, my_lse, red);
+    if (threadIdx.x >= 32) return;
 
     // ---- 2. push to every rank's gather buffer (own included), then publish the epoch
     const int parity = (int)(epoch & 1u);
@@ -184,7 +152,7 @@ __global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__
     }
     if (lane == 0 && p.lse_out) p.lse_out[row] = glse;
 
-    // ---- 5. the last warp of the grid closes the step: every warp has read the epoch before it got here
+    // ---- 5. the last row of the grid closes the step: every CTA has read the epoch before it got here
     __syncwarp();
     if (lane == 0) {
         __threadfence();
@@ -199,11 +167,11 @@ __global__ void __launch_bounds__(128) xchg_merge_kernel(const __grid_constant__
 }  // namespace
 
 cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream) {
-    dim3 grid((p.rows + 3) / 4);
+    dim3 grid(p.rows);
     if (is_bf16)
-        xchg_merge_kernel<__nv_bfloat16><<<grid, 128, 0, stream>>>(p);
+        xchg_merge_kernel<__nv_bfloat16><<<grid, kMergeThreads, 0, stream>>>(p);
     else
-        xchg_merge_kernel<__half><<<grid, 128, 0, stream>>>(p);
+        xchg_merge_kernel<__half><<<grid, kMergeThreads, 0, stream>>>(p);
     return cudaGetLastError();
 }
 
