@@ -215,6 +215,7 @@ def main():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-long-context", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -313,6 +314,39 @@ def main():
                       "roofline": {"bound": "hbm", "achieved": round(gbs, 1), "peak": pk["hbm"], "unit": "GB/s",
                                    "frac": round(gbs / pk["hbm"], 4), "traffic": profile_traffic("decode")}}
 
+        # ---- long-context decode, KV axis sharded over the ranks (BASELINE.json configs[4]; ours only): 1M rows in total,
+        # exchange fused into the merge kernel over NVLink peer memory (no NCCL call on the data path).  STRONG scaling:
+        # the total work is fixed, so `value` is the aggregate GB/s of the whole 1M-row problem.
+        long_ctx = None
+        if args.impl == "ours" and not args.no_long_context:
+            try:
+                from mini_flash_attention_b200 import parallel as par
+                del dq, kc, vc, bt, sl
+                torch.cuda.empty_cache()
+                lB, lHq, lHkv, lKV, lpage = 1, 32, 8, 1 << 20, 256
+                rows = par.kv_shard_rows(lKV, world, align=lpage)
+                lnb = lB * rows // lpage
+                lq = torch.randn(lB, 1, lHq, dD, device="cuda", dtype=dt, generator=torch.Generator(device="cuda").manual_seed(7))
+                lk = torch.randn(lnb, lpage, lHkv, dD, device="cuda", dtype=dt)
+                lv = torch.randn(lnb, lpage, lHkv, dD, device="cuda", dtype=dt)
+                lbt = torch.randperm(lnb, device="cuda").reshape(lB, rows // lpage).int()
+                lsl = par.kv_shard_lengths(torch.full((lB,), lKV, dtype=torch.int32, device="cuda"), rank, rows)
+                xchg = par.KVShardExchange(world, rank, lB * lHq, dD)
+                lfn = lambda: par.decode_kv_sharded(lq, lk, lv, lsl, lbt, world=world, exchange=xchg)  # noqa: E731
+                lms = time_steps(lfn, max(args.steps, 30), max(args.warmup, 5), world)
+                st = xchg.status()
+                lbytes = 2.0 * lB * lKV * lHkv * dD * 2
+                lgbs = lbytes / (lms * 1e-3) / 1e9
+                long_ctx = {"workload": f"decode B1 Hq32 Hkv8 D128 KV=1M rows sharded over {world} GPU(s), paged(256)",
+                            "scaling": "strong", "ms_per_step": round(lms, 4), "value": round(lgbs, 1), "unit": "GB/s",
+                            "per_gpu": round(lgbs / world, 1), "frac_of_hbm_peak_per_gpu": round(lgbs / world / pk["hbm"], 4),
+                            "exchange": "fused into the merge kernel: P2P push + flag over NVLink, no NCCL call",
+                            "exchange_timeout_status": st, "launches_per_step": 2}
+                xchg.close()
+                del lk, lv
+            except Exception as e:  # the headline legs above stay valid
+                long_ctx = {"error": f"{type(e).__name__}: {e}"[:300]}
+
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
@@ -336,6 +370,8 @@ def main():
         out["e2e"] = e2e
     if decode is not None:
         out["decode"] = decode
+    if long_ctx is not None:
+        out["long_context_decode"] = long_ctx
     if args.impl == "reference":
         out["impl"] = "reference"
         out["cpu_baseline"] = {"value": out["value"], "unit": "TFLOP/s", "cores": 0, "kind": "reference",

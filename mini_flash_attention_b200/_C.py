@@ -495,5 +495,14 @@ if _shim is not None:
         return _shim.mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal,
                                                            num_splits, return_lse, k_new, v_new)
 
+    _py_decode_kv_sharded_fused = decode_kv_sharded_fused
+
+    def decode_kv_sharded_fused(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, xchg_handle, return_lse=False):  # noqa: F811
+        if return_lse or not hasattr(_shim, "decode_kv_sharded_fused"):
+            return _py_decode_kv_sharded_fused(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, xchg_handle, return_lse)
+        if isinstance(cache_seqlens, int):
+            cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
+        return _shim.decode_kv_sharded_fused(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, xchg_handle)
+
     mini_flash_attention_with_kvcache.__doc__ = _py_with_kvcache.__doc__
     decode_partial.__doc__ = _py_decode_partial.__doc__

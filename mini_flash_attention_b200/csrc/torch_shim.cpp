@@ -412,6 +412,30 @@ std::tuple<at::Tensor, at::Tensor> decode_partial(const at::Tensor& q, const at:
     return {o, lse};
 }
 
+// KV-sharded decode with the exchange fused into the merge kernel (include/mfa_b200.h mfa_decode_fwd_kv_sharded,
+// csrc/xchg_sm100.cu): this rank's rows of the KV axis in, the full result (B,1,H,D) out on every rank.  `xchg` is a
+// connected mfa_xchg_t* passed as an integer (parallel.KVShardExchange.handle).
+at::Tensor decode_kv_sharded_fused(const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache,
+                                   std::optional<at::Tensor> cache_seqlens, std::optional<at::Tensor> block_table,
+                                   int64_t num_splits, int64_t xchg) {
+    DecodeCall c;
+    decode_params(c, q, k_cache, v_cache, cache_seqlens, block_table, num_splits);
+    TORCH_CHECK(c.P.seqlen_k > 0 && q.numel() > 0, "KV-sharded decode needs a non-empty problem");
+    TORCH_CHECK(xchg != 0, "null exchange handle");
+    c10::cuda::CUDAGuard guard(q.device());
+    at::Tensor out = at::empty(q.sizes(), q.options());
+    c.P.o_ptr = out.data_ptr();
+    c.P.o_batch_stride = out.stride(0); c.P.o_row_stride = out.stride(1); c.P.o_head_stride = out.stride(2);
+    const int splits = mfa_decode_num_splits(&c.P);
+    TORCH_CHECK(splits >= 1, "mfa_decode_num_splits failed: ", mfa_last_error());
+    c.P.num_splits = splits;
+    const size_t ws_bytes = mfa_decode_kv_sharded_workspace_bytes(&c.P, splits);
+    at::Tensor ws = at::empty({(int64_t)(ws_bytes / 4)}, q.options().dtype(at::kFloat));
+    check_rc(mfa_decode_fwd_kv_sharded(&c.P, ws.data_ptr(), ws_bytes, reinterpret_cast<mfa_xchg_t*>(xchg), stream_of(q)),
+             "mfa_decode_fwd_kv_sharded");
+    return out;
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.doc() = "mini_flash_attention_b200 compiled host shim over libmfa_b200.so";
     namespace py = pybind11;
@@ -445,6 +469,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("mini_flash_attention_with_kvcache_ext", &mini_flash_attention_with_kvcache_ext, py::arg("q"),
           py::arg("k_cache"), py::arg("v_cache"), py::arg("cache_seqlens"), py::arg("block_table"), py::arg("causal"),
           py::arg("num_splits"), py::arg("return_lse"), py::arg("k_new"), py::arg("v_new"));
+    m.def("decode_kv_sharded_fused", &decode_kv_sharded_fused, py::arg("q"), py::arg("k_cache"), py::arg("v_cache"),
+          py::arg("cache_seqlens"), py::arg("block_table"), py::arg("num_splits"), py::arg("xchg"));
     m.def("decode_partial", &decode_partial, py::arg("q"), py::arg("k_cache"), py::arg("v_cache"),
           py::arg("cache_seqlens"), py::arg("block_table"), py::arg("num_splits") = 0);
 }
