@@ -95,7 +95,8 @@ typedef struct mfa_params {
      * col <= row + (len_k - len_q), per sequence (flash-attn >= 2.1 convention; what chunked prefill against a longer
      * cache needs).  0 = the reference's top-left mask (prefill.cuh:416).  New. */
     int32_t causal_bottom_right;
-    /* Prefill only: HONOUR window_size_left / window_size_right as a sliding-window (band) mask -- key col visible iff
+    /* HONOUR window_size_left / window_size_right as a sliding-window (band) mask (decode: the query sits at position
+     * len - 1 and sees the last window_size_left + 1 keys; window_size_right is irrelevant).  Prefill: -- key col visible iff
      * row + shift - left <= col <= row + shift + right, a bound < 0 absent, is_causal forcing right = 0; shift = 0
      * (top-left, the reference's alignment) or len_k - len_q per sequence when causal_bottom_right is set (flash-attn's
      * window_size convention).  KV tiles outside the band are skipped.  0 = the reference's behaviour: the two window

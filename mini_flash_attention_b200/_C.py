@@ -251,10 +251,13 @@ def _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits):
 
 
 def mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens: Optional[Union[int, torch.Tensor]],
-                                      block_table, causal, num_splits=0, _want_lse=False, _k_new=None, _v_new=None):
+                                      block_table, causal, num_splits=0, _want_lse=False, _k_new=None, _v_new=None,
+                                      _window_left=-1):
     """q_len == 1 decode over a contiguous or paged KV cache.  api.cpp:343-446.
     `causal` is accepted and ignored exactly like the reference (api.cpp:349, quirk Q10)."""
     P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
+    if _window_left is not None and _window_left >= 0:  # sliding window (SURVEY 8f row 3): the last window_left + 1 keys
+        P.local_window, P.window_size_left, P.window_size_right = 1, int(_window_left), -1
     if _k_new is not None or _v_new is not None:
         keep.append(_append_kv(P, keep, q, k_cache, v_cache, cache_seqlens, _k_new, _v_new))
     out = torch.empty_like(q)  # api.cpp:405
@@ -428,9 +431,9 @@ def mini_flash_attention_varlen_forward_ext(q, k, v, cu_seqlens_q, cu_seqlens_k,
 
 
 def mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits, return_lse,
-                                          k_new, v_new):
+                                          k_new, v_new, window_left=-1):
     r = _py_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits, _want_lse=return_lse,
-                         _k_new=k_new, _v_new=v_new)
+                         _k_new=k_new, _v_new=v_new, _window_left=window_left)
     return r if return_lse else (r, None)
 
 
@@ -489,11 +492,11 @@ if _shim is not None:
     mini_flash_attention_varlen_forward_ext = _shim.mini_flash_attention_varlen_forward_ext
 
     def mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits,
-                                              return_lse, k_new, v_new):
+                                              return_lse, k_new, v_new, window_left=-1):
         if isinstance(cache_seqlens, int):
             cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
         return _shim.mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal,
-                                                           num_splits, return_lse, k_new, v_new)
+                                                           num_splits, return_lse, k_new, v_new, window_left)
 
     _py_decode_kv_sharded_fused = decode_kv_sharded_fused
 

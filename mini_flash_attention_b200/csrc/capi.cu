@@ -405,6 +405,7 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
     kp.num_splits = splits;
     kp.head_tiles = (kp.group + mfa::kDecodeMaxGroup - 1) / mfa::kDecodeMaxGroup;
     kp.partial_out = (p->partial_out || x) ? 1 : 0;
+    kp.window_left = (p->local_window && p->window_size_left >= 0) ? p->window_size_left : -1;
     kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);
     kp.scale_log2 = kp.scale * 1.4426950408889634f;
 

@@ -114,8 +114,12 @@ __global__ void __launch_bounds__(kDecodeThreads) decode_splitkv_kernel(const __
 
     const int len = p.seqlens_k ? min(p.seqlens_k[b], p.seqlen_k) : p.seqlen_k;
     const int n_blocks = (len + kTile - 1) / kTile;
-    const int per_split = (n_blocks + p.num_splits - 1) / p.num_splits;   // decode.cuh:27
-    const int t0 = split * per_split;
+    // sliding window: the single query sits at position len - 1 and sees keys [first_key, len); tiles in
+    // front of the window are not loaded and the splits partition only the tiles of the window
+    const int first_key = (p.window_left >= 0) ? max(len - 1 - p.window_left, 0) : 0;
+    const int tile_lo = first_key / kTile;
+    const int per_split = (n_blocks - tile_lo + p.num_splits - 1) / p.num_splits;   // decode.cuh:27
+    const int t0 = tile_lo + split * per_split;
     const int t1 = min(n_blocks, t0 + per_split);
     const int ntiles = max(t1 - t0, 0);
 
@@ -242,6 +246,14 @@ __global__ void __launch_bounds__(kDecodeThreads) decode_splitkv_kernel(const __
                 const int kv = wrow + nt * 8 + tq * 2;
                 if (kv >= rows_valid) sc[nt][0] = sc[nt][2] = -INFINITY;
                 if (kv + 1 >= rows_valid) sc[nt][1] = sc[nt][3] = -INFINITY;
+            }
+        }
+        if (row0 < first_key) {   // head of the sliding window: keys in front of it
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+                const int kv = row0 + wrow + nt * 8 + tq * 2;
+                if (kv < first_key) sc[nt][0] = sc[nt][2] = -INFINITY;
+                if (kv + 1 < first_key) sc[nt][1] = sc[nt][3] = -INFINITY;
             }
         }
         // ---- online softmax (exp2 domain), two head rows per thread

@@ -29,6 +29,7 @@ struct DecodeKParams {
     int32_t num_splits;
     int32_t head_tiles;        // ceil(group / 16)
     int32_t partial_out;
+    int32_t window_left;       // >= 0: sliding window, the query (position len - 1) sees keys >= len - 1 - window_left; < 0: all
     float scale, scale_log2;
 };
 

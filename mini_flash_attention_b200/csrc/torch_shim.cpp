@@ -323,9 +323,15 @@ static std::tuple<at::Tensor, at::Tensor> kvcache_impl(const at::Tensor& q, cons
                                                        const std::optional<at::Tensor>& block_table, int64_t num_splits,
                                                        bool want_lse,
                                                        const std::optional<at::Tensor>& k_new = std::nullopt,
-                                                       const std::optional<at::Tensor>& v_new = std::nullopt) {
+                                                       const std::optional<at::Tensor>& v_new = std::nullopt,
+                                                       int64_t window_left = -1) {
     DecodeCall c;
     decode_params(c, q, k_cache, v_cache, cache_seqlens, block_table, num_splits);
+    if (window_left >= 0) {   // sliding window: the last window_left + 1 keys
+        c.P.local_window = 1;
+        c.P.window_size_left = (int32_t)window_left;
+        c.P.window_size_right = -1;
+    }
     c10::cuda::CUDAGuard guard(q.device());
     at::Tensor seqlens_new;
     if (k_new.has_value() || v_new.has_value()) {
@@ -390,8 +396,8 @@ std::tuple<at::Tensor, at::Tensor> mini_flash_attention_with_kvcache_lse(
 std::tuple<at::Tensor, std::optional<at::Tensor>> mini_flash_attention_with_kvcache_ext(
     const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache, std::optional<at::Tensor> cache_seqlens,
     std::optional<at::Tensor> block_table, bool /*causal*/, int64_t num_splits, bool return_lse,
-    std::optional<at::Tensor> k_new, std::optional<at::Tensor> v_new) {
-    auto r = kvcache_impl(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, return_lse, k_new, v_new);
+    std::optional<at::Tensor> k_new, std::optional<at::Tensor> v_new, int64_t window_left) {
+    auto r = kvcache_impl(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, return_lse, k_new, v_new, window_left);
     return {std::get<0>(r), return_lse ? std::optional<at::Tensor>(std::get<1>(r)) : std::nullopt};
 }
 
@@ -468,7 +474,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("block_table"), py::arg("return_lse"), py::arg("bottom_right"));
     m.def("mini_flash_attention_with_kvcache_ext", &mini_flash_attention_with_kvcache_ext, py::arg("q"),
           py::arg("k_cache"), py::arg("v_cache"), py::arg("cache_seqlens"), py::arg("block_table"), py::arg("causal"),
-          py::arg("num_splits"), py::arg("return_lse"), py::arg("k_new"), py::arg("v_new"));
+          py::arg("num_splits"), py::arg("return_lse"), py::arg("k_new"), py::arg("v_new"), py::arg("window_left") = -1);
     m.def("decode_kv_sharded_fused", &decode_kv_sharded_fused, py::arg("q"), py::arg("k_cache"), py::arg("v_cache"),
           py::arg("cache_seqlens"), py::arg("block_table"), py::arg("num_splits"), py::arg("xchg"));
     m.def("decode_partial", &decode_partial, py::arg("q"), py::arg("k_cache"), py::arg("v_cache"),

@@ -117,6 +117,7 @@ def flash_attn_with_kvcache(
     return_lse: bool = False,
     k: Optional[torch.Tensor] = None,
     v: Optional[torch.Tensor] = None,
+    window_size: Tuple[int, int] = (-1, -1),
 ):
     """Single-token decode against a KV cache (reference: interface.py:95-124).
 
@@ -132,13 +133,17 @@ def flash_attn_with_kvcache(
             does not implement) (batch_size, seqlen_new, nheads_k, headdim) new keys/values: written IN PLACE into the
             cache at positions cache_seqlens[b] .. + seqlen_new - 1 (through block_table when paged) before the
             attention, which then covers cache_seqlens + seqlen_new keys.  cache_seqlens itself is not modified.
+        window_size: (new -- SURVEY 8f row 3) sliding window (left, right): the query sits at the last position and
+            attends to the last ``left + 1`` keys only (right is irrelevant for one query); KV tiles in front of the
+            window are not read, so the step costs O(window), not O(cache_seqlens).  -1 = unbounded.
         return_lse: (new) also return softmax_lse (batch_size, nheads, 1) fp32 -- the tensor the reference allocates
             and drops (api.cpp:436-437)
     """
     assert q.size(1) == 1, "flash_attn_with_kvcache currently only supports seqlen_q=1 for decoding"
-    if k is not None or v is not None:
+    wl, _ = _window(window_size)
+    if k is not None or v is not None or wl >= 0:
         out, lse = _C.mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal,
-                                                            num_splits, return_lse, k, v)
+                                                            num_splits, return_lse, k, v, wl)
         return (out, lse) if return_lse else out
     if return_lse:
         return _C.mini_flash_attention_with_kvcache_lse(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)

@@ -115,7 +115,7 @@ def varlen_ref(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, block_table=No
     return out
 
 
-def kvcache_ref(q, k_cache, v_cache, cache_seqlens=None, block_table=None, return_lse=False):
+def kvcache_ref(q, k_cache, v_cache, cache_seqlens=None, block_table=None, return_lse=False, window_left=-1):
     """q (B,1,H,D); contiguous cache (B,Sk,Hkv,D) or paged (num_blocks,page,Hkv,D) + block_table."""
     B, _, H, D = q.shape
     out = torch.zeros(q.shape, dtype=torch.float32, device=q.device)
@@ -139,6 +139,8 @@ def kvcache_ref(q, k_cache, v_cache, cache_seqlens=None, block_table=None, retur
         else:
             kb = k_cache[b:b + 1, :L]
             vb = v_cache[b:b + 1, :L]
+        if window_left >= 0:   # sliding window: the query at position L - 1 sees the last window_left + 1 keys
+            kb, vb = kb[:, max(L - 1 - window_left, 0):], vb[:, max(L - 1 - window_left, 0):]
         out[b:b + 1] = attention_ref(q[b:b + 1], kb, vb)
         if return_lse:
             Hkv = kb.shape[2]

@@ -77,7 +77,8 @@ def test_python_surface_matches_reference():
     assert kw_only(m.flash_attn_varlen_func) == {"return_lse": False, "bottom_right": False, "window_size": (-1, -1)}
     sig = inspect.signature(m.flash_attn_with_kvcache)
     assert positional(m.flash_attn_with_kvcache) == ["q", "k_cache", "v_cache", "cache_seqlens", "block_table", "num_splits"]
-    assert kw_only(m.flash_attn_with_kvcache) == {"causal": False, "return_lse": False, "k": None, "v": None}
+    assert kw_only(m.flash_attn_with_kvcache) == {"causal": False, "return_lse": False, "k": None, "v": None,
+                                                     "window_size": (-1, -1)}
     assert sig.parameters["num_splits"].default == 0
     for name in ("mini_flash_attention_forward", "mini_flash_attention_varlen_forward", "mini_flash_attention_with_kvcache"):
         assert hasattr(m._C, name)

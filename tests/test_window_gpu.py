@@ -125,3 +125,66 @@ def test_window_cost_scales_with_the_window():
     t_full = t(lambda: mfa.flash_attn_func(q, k, v, causal=True))
     t_win = t(lambda: mfa.flash_attn_func(q, k, v, causal=True, window_size=(255, 0)))
     assert t_win < 0.35 * t_full, (t_win, t_full)
+
+
+@pytest.mark.parametrize("B,H,Hkv,D,lens,page,dt", [
+    (3, 8, 2, 128, [4096, 130, 1], 256, torch.float16),
+    (2, 32, 8, 128, [5000, 777], 64, torch.bfloat16),
+    (2, 16, 16, 64, [300, 2048], None, torch.float16),      # contiguous cache
+    (1, 4, 1, 256, [1500], 64, torch.bfloat16),
+])
+@pytest.mark.parametrize("wl", [0, 1, 63, 64, 200, 1000, 100000])
+@pytest.mark.parametrize("splits", [0, 1, 3])
+def test_window_decode(B, H, Hkv, D, lens, page, dt, wl, splits):
+    """Decode with a sliding window: the single query sees the last wl + 1 keys; tiles in front are skipped."""
+    import mini_flash_attention as mfa
+    from oracle import ref_attention as R
+    g = torch.Generator(device="cuda").manual_seed(11)
+    cap = max(lens)
+    q = torch.randn(B, 1, H, D, device="cuda", dtype=dt, generator=g)
+    sl = torch.tensor(lens, dtype=torch.int32, device="cuda")
+    if page is None:
+        kc = torch.randn(B, cap, Hkv, D, device="cuda", dtype=dt, generator=g)
+        vc = torch.randn(B, cap, Hkv, D, device="cuda", dtype=dt, generator=g)
+        bt = None
+    else:
+        per = (cap + page - 1) // page
+        kc = torch.randn(B * per, page, Hkv, D, device="cuda", dtype=dt, generator=g)
+        vc = torch.randn(B * per, page, Hkv, D, device="cuda", dtype=dt, generator=g)
+        bt = torch.randperm(B * per, device="cuda", generator=g).int().reshape(B, per)
+    out, lse = mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt, splits, window_size=(wl, -1), return_lse=True)
+    ref, lref = R.kvcache_ref(q, kc, vc, sl, bt, return_lse=True, window_left=wl)
+    assert (out.float() - ref).abs().max().item() <= TOL[dt]
+    assert (lse.view(B, H) - lref).abs().max().item() <= 2e-3
+    if wl >= cap:
+        assert torch.equal(out, mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt, splits))
+
+
+def test_window_decode_cost_and_shims():
+    import mini_flash_attention as mfa
+    from mini_flash_attention_b200 import _C
+    dt = torch.bfloat16
+    B, H, D, KV, page = 24, 24, 128, 8192, 256
+    g = torch.Generator(device="cuda").manual_seed(3)
+    q = torch.randn(B, 1, H, D, device="cuda", dtype=dt, generator=g)
+    kc = torch.randn(B * KV // page, page, H, D, device="cuda", dtype=dt, generator=g)
+    vc = torch.randn(B * KV // page, page, H, D, device="cuda", dtype=dt, generator=g)
+    bt = torch.randperm(B * KV // page, device="cuda", generator=g).int().reshape(B, KV // page)
+    sl = torch.full((B,), KV, dtype=torch.int32, device="cuda")
+    a, la = _C.mini_flash_attention_with_kvcache_ext(q, kc, vc, sl, bt, False, 0, True, None, None, 511)
+    b, lb = _C._py_with_kvcache_ext(q, kc, vc, sl, bt, False, 0, True, None, None, 511)
+    assert torch.equal(a, b) and torch.equal(la, lb)
+
+    def t(fn):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 20
+    t_full = t(lambda: mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt))
+    t_win = t(lambda: mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt, window_size=(511, -1)))
+    assert t_win < 0.4 * t_full, (t_win, t_full)
