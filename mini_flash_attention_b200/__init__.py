@@ -8,6 +8,8 @@ from mini_flash_attention_b200.interface import (
     flash_attn_with_kvcache,
 )
 
+from mini_flash_attention_b200.host import flash_attn_func_host  # noqa: E402  (host-buffer pipeline; new)
+
 __all__ = [
     "flash_attn_func",
     "flash_attn_varlen_func",
