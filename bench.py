@@ -279,7 +279,7 @@ def main():
             if args.impl == "ours" and not args.e2e_sequential:
                 # the repo's host-buffer entry point: H2D / kernel / D2H pipelined over batch chunks on three streams
                 from mini_flash_attention_b200.host import flash_attn_func_host
-                e2e_method = "flash_attn_func_host: H2D | kernel | D2H pipelined over 8 batch chunks, 3 streams"
+                e2e_method = "flash_attn_func_host: H2D | kernel | D2H pipelined over 16 batch chunks, 3 streams"
 
                 def step_e2e():
                     flash_attn_func_host(hq, hk, hv, False, out=ho)

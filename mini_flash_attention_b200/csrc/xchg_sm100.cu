@@ -167,6 +167,19 @@ __global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_
 }  // namespace
 
 cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream) {
+    // The kernel spins until the peers arrive, so it must never stand in the way of the kernels it is waiting for.  An SM
+    // re-partitions L1 / shared memory only when idle: a grid of these CTAs (8 KB static smem, small carve-out) on every
+    // SM would block a split-KV kernel (100+ KB dynamic smem) of ANOTHER rank that shares the GPU (ranks as streams of
+    // one process, tests/test_kv_exchange_gpu.py: seen as a timeout with 8 ranks x 32 rows).  Asking for the maximum
+    // shared-memory carve-out keeps both kernels in the same SM configuration.
+    static bool attr_done[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && !attr_done[dev]) {
+        cudaFuncSetAttribute(xchg_merge_kernel<__nv_bfloat16>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(xchg_merge_kernel<__half>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        attr_done[dev] = true;
+    }
     dim3 grid(p.rows);
     if (is_bf16)
         xchg_merge_kernel<__nv_bfloat16><<<grid, kMergeThreads, 0, stream>>>(p);

@@ -47,7 +47,7 @@ def flash_attn_func_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, caus
 
     The call is asynchronous with respect to the host like any CUDA op: the current stream of `device` waits for the last
     copy-out, so `torch.cuda.current_stream().synchronize()` (or an event recorded after the call) means `out` is ready.
-    chunk_batch: batch elements per pipeline stage (default: about 1/8 of the batch); depth: chunks in flight."""
+    chunk_batch: batch elements per pipeline stage (default: about 1/16 of the batch; scripts/host_chunks.py); depth: chunks in flight."""
     if q.is_cuda or k.is_cuda or v.is_cuda:
         raise RuntimeError("flash_attn_func_host takes host tensors; use flash_attn_func for CUDA tensors")
     if q.dim() != 4 or k.dim() != 4 or v.dim() != 4:
@@ -64,7 +64,7 @@ def flash_attn_func_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, caus
         raise RuntimeError("out must be a host tensor with q's shape and dtype")
     if B == 0 or q.numel() == 0:
         return out
-    cb = chunk_batch if chunk_batch else max(1, (B + 7) // 8)
+    cb = chunk_batch if chunk_batch else max(1, (B + 15) // 16)
     cb = min(cb, B)
     key = (device, q.dtype, (cb,) + tuple(q.shape[1:]), (cb,) + tuple(k.shape[1:]), depth)
     sl = _slots.get(key)
