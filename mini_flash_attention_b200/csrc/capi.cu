@@ -248,17 +248,24 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
 }
 
 // ------------------------------------------------------------------------------------------ decode
+#ifndef MFA_DECODE_CTAS_PER_SM
+// CTAs per SM the split heuristic plans for.  Three fit with the 2-stage ring (decode_sm100.cu), but planning for two is
+// what measures best (scripts/decode_stages.py, B=24 GQA 32/8: KV=512 12.3 us vs 18.9 us, KV=8192 127 vs 138 us, and the
+// B=1 long-context step 16.5 vs 20.6 us at 16K rows): more, thinner splits cost more in the merge than the fuller last
+// wave gives back.
+#define MFA_DECODE_CTAS_PER_SM 2
+#endif
 static int decode_splits_for(const mfa_params_t* p) {
     const int block_n = mfa::kDecodeTileRows;   // api.cpp:314-315
     const int num_n_blocks = std::max(1, (p->seqlen_k + block_n - 1) / block_n);
     int splits = p->num_splits;
     if (splits < 1) {
         // Heuristic in the spirit of api.cpp:269-302, re-derived for this kernel: one CTA serves a whole GQA
-        // group, two CTAs are resident per SM, and a split should keep >= 4 tiles (256 rows) of work.
+        // group, two CTAs per SM are planned for (see above), and a split should keep >= 4 tiles (256 rows) of work.
         const int group = p->heads / p->kv_heads;
         const int head_tiles = (group + mfa::kDecodeMaxGroup - 1) / mfa::kDecodeMaxGroup;
         const int base = p->batch * p->kv_heads * head_tiles;
-        const int slots = 2 * sm_count();
+        const int slots = MFA_DECODE_CTAS_PER_SM * sm_count();
         if (base * 10 >= slots * 8) {
             splits = 1;
         } else {

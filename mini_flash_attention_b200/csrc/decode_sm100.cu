@@ -80,12 +80,18 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk) {
     return static_cast<uint32_t>((chunk >> 3) * (ROWS * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4));
 }
 
+#ifndef MFA_DECODE_STAGES
+// Ring depth at head_dim 128/256.  2 stages = 64 KB per CTA = THREE CTAs per SM (the same 192 KB in flight per SM as 3
+// stages x 2 CTAs): one more CTA's prologue / epilogue hides under the others' streaming, +1-2 % at every KV length of
+// the B=24 sweep (scripts/decode_stages.py: 7045 -> 7181 GB/s at KV=8192, 4819 -> 4903 at KV=512).
+#define MFA_DECODE_STAGES 2
+#endif
 template <int DPAD>
 struct DecodeCfg {
     static constexpr int kTile = kDecodeTileRows;
     static constexpr int kTileBytes = kTile * DPAD * 2;          // one of K or V
     static constexpr int kStageBytes = 2 * kTileBytes;           // K then V
-    static constexpr int kStages = (DPAD == 64) ? 6 : 3;
+    static constexpr int kStages = (DPAD == 64) ? 2 * MFA_DECODE_STAGES : MFA_DECODE_STAGES;
     static constexpr int kRingBytes = kStages * kStageBytes;
     static constexpr int kSmemBytes = kRingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
