@@ -249,10 +249,9 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
 
 // ------------------------------------------------------------------------------------------ decode
 #ifndef MFA_DECODE_CTAS_PER_SM
-// CTAs per SM the split heuristic plans for.  Three fit with the 2-stage ring (decode_sm100.cu), but planning for two is
-// what measures best (scripts/decode_stages.py, B=24 GQA 32/8: KV=512 12.3 us vs 18.9 us, KV=8192 127 vs 138 us, and the
-// B=1 long-context step 16.5 vs 20.6 us at 16K rows): more, thinner splits cost more in the merge than the fuller last
-// wave gives back.
+// CTAs per SM the split heuristic plans for: two are resident (162 registers at head_dim 128, decode_sm100.cu).
+// Planning for three was measured and is worse (scripts/decode_stages.py, B=24 GQA 32/8: KV=512 18.9 us vs 12.3 us,
+// KV=8192 138 vs 127 us; B=1 long-context step at 16K rows 20.6 vs 16.5 us).
 #define MFA_DECODE_CTAS_PER_SM 2
 #endif
 static int decode_splits_for(const mfa_params_t* p) {

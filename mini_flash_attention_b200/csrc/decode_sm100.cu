@@ -81,9 +81,10 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk) {
 }
 
 #ifndef MFA_DECODE_STAGES
-// Ring depth at head_dim 128/256.  2 stages = 64 KB per CTA = THREE CTAs per SM (the same 192 KB in flight per SM as 3
-// stages x 2 CTAs): one more CTA's prologue / epilogue hides under the others' streaming, +1-2 % at every KV length of
-// the B=24 sweep (scripts/decode_stages.py: 7045 -> 7181 GB/s at KV=8192, 4819 -> 4903 at KV=512).
+// Ring depth at head_dim 128/256.  Measured, not derived (scripts/decode_stages.py, B=24 sweep): 2 stages (64 KB per
+// CTA) beat 3 stages by 1-3 % at every KV length (7045 -> 7262 GB/s at KV=8192, 4819 -> 4896 at KV=512).  Residency
+// stays at TWO CTAs per SM either way -- the kernel uses 162 registers at head_dim 128 -- and forcing three with
+// __launch_bounds__(160, 3) (128 registers, -DMFA_DECODE_MINBLOCKS=3) is 13 % slower (6313 GB/s at KV=8192).
 #define MFA_DECODE_STAGES 2
 #endif
 template <int DPAD>
@@ -96,8 +97,11 @@ struct DecodeCfg {
     static constexpr int kSmemBytes = kRingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+#ifndef MFA_DECODE_MINBLOCKS
+#define MFA_DECODE_MINBLOCKS 1
+#endif
 template <typename T, int DPAD>
-__global__ void __launch_bounds__(kDecodeThreads) decode_splitkv_kernel(const __grid_constant__ CUtensorMap tmK,
+__global__ void __launch_bounds__(kDecodeThreads, (DPAD <= 128) ? MFA_DECODE_MINBLOCKS : 1) decode_splitkv_kernel(const __grid_constant__ CUtensorMap tmK,
                                                                         const __grid_constant__ CUtensorMap tmV,
                                                                         const __grid_constant__ DecodeKParams p) {
     using Cfg = DecodeCfg<DPAD>;
