@@ -203,7 +203,7 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
 // tiles are still in the softmax, and the epilogue of item n overlaps the first S MMAs of item n+1.  (Measured before:
 // ~7 k cycles from CTA start to the first S and ~3 k of epilogue per ~115 k-cycle item at S=4096, 22 % at S=1024.)
 // All mbarrier parities therefore come from RUNNING counters: items done (q_full / q_empty) and tiles done per Q tile.
-template <typename T, int DPAD>
+template <typename T, int DPAD, bool kPoly>
 __global__ void __launch_bounds__(kPrefillThreads, 1)
     prefill_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const __grid_constant__ PrefillKParams p) {
@@ -574,7 +574,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                         const int e = hf * 64 + 2 * c;
                         uint64_t x2 = f2_fma(f2_pack(__uint_as_float(su[e]), __uint_as_float(su[e + 1])), c2_2, nms_2);
                         uint64_t p2;
-                        if ((Cfg::kPolyMask >> (c & 3)) & 1) {
+                        if (kPoly && ((Cfg::kPolyMask >> (c & 3)) & 1)) {
                             p2 = exp2_poly2(x2);
                         } else {
                             float x0, x1;
@@ -658,14 +658,23 @@ template <typename T, int DPAD>
 static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                     const PrefillKParams& p, cudaStream_t stream) {
     using Cfg = PrefillCfg<DPAD>;
-    auto kern = prefill_fwd_kernel<T, DPAD>;
-    static bool attr_done[64] = {};
+    // exp2 placement.  A quarter of the exponentials on the FMA pipe (polynomial) is faster while the SM clock is high:
+    // +2 % at S=1024 (0.68 ms launches).  A launch of several ms runs into the board power cap (sw_power_cap,
+    // 1.59-1.68 GHz), where the extra FMA work costs more clock than the relieved MUFU gives: all-MUFU is +1.5 % at the
+    // headline S=4096 (9 ms) and +2-3 % causal (scripts/tune_prefill.py, r01g).  So: by the work of the launch.
+    // MFA_PREFILL_POLY=0/1 forces one form (tuning aid).
+    static const int poly_env = [] { const char* e = getenv("MFA_PREFILL_POLY"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
+    const double mflop = 4e-6 * (double)p.batch * p.heads * (double)p.seqlen_q * (double)p.seqlen_k * (double)DPAD *
+                         (p.has_hi ? 0.5 : 1.0);
+    const bool poly = poly_env >= 0 ? (poly_env == 1) : (mflop < 3.0e6);   // < ~3 TFLOP per launch (~3 ms)
+    auto kern = poly ? prefill_fwd_kernel<T, DPAD, true> : prefill_fwd_kernel<T, DPAD, false>;
+    static bool attr_done[64][2] = {};
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 64 && !attr_done[dev]) {
+    if (dev < 64 && !attr_done[dev][poly]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
         if (e != cudaSuccess) return e;
-        attr_done[dev] = true;
+        attr_done[dev][poly] = true;
     }
     // Fixed-length batches run PERSISTENT: one CTA per SM walks the work items (m-block fastest, so that the CTAs
     // running at the same time share K/V in L2).  With the causal mask an item's cost grows with its m-block, and a
