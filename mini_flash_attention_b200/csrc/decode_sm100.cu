@@ -97,11 +97,16 @@ struct DecodeCfg {
     static constexpr int kSmemBytes = kRingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-#ifndef MFA_DECODE_MINBLOCKS
-#define MFA_DECODE_MINBLOCKS 1
+// (tuning aid: -DMFA_DECODE_MINBLOCKS=3 adds a min-blocks launch bound at head_dim <= 128.  Even a bound of 1 changes
+//  ptxas' allocation -- 180 instead of 162 registers -- and costs 28 % at KV=8192 (436 vs 340 us, profiles r01h vs r01g),
+//  so the default build states NO min-blocks bound at all.)
+#ifdef MFA_DECODE_MINBLOCKS
+#define MFA_DECODE_BOUNDS(DP) __launch_bounds__(kDecodeThreads, ((DP) <= 128) ? MFA_DECODE_MINBLOCKS : 1)
+#else
+#define MFA_DECODE_BOUNDS(DP) __launch_bounds__(kDecodeThreads)
 #endif
 template <typename T, int DPAD>
-__global__ void __launch_bounds__(kDecodeThreads, (DPAD <= 128) ? MFA_DECODE_MINBLOCKS : 1) decode_splitkv_kernel(const __grid_constant__ CUtensorMap tmK,
+__global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_constant__ CUtensorMap tmK,
                                                                         const __grid_constant__ CUtensorMap tmV,
                                                                         const __grid_constant__ DecodeKParams p) {
     using Cfg = DecodeCfg<DPAD>;
