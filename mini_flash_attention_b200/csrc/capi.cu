@@ -265,7 +265,11 @@ static int decode_splits_for(const mfa_params_t* p) {
         const int head_tiles = (group + mfa::kDecodeMaxGroup - 1) / mfa::kDecodeMaxGroup;
         const int base = p->batch * p->kv_heads * head_tiles;
         const int slots = MFA_DECODE_CTAS_PER_SM * sm_count();
-        if (base * 10 >= slots * 8) {
+        // No split when the grid already fills 80 % of the slots -- or has at least one CTA per SM and a short KV axis:
+        // one CTA keeps 64 KB in flight, which is enough to pull an SM's share of HBM, so B=24 GQA 32/8 (192 CTAs on
+        // 148 SMs) is already within ~10 % of the HBM time unsplit, and the split form only adds the merge launch
+        // (scripts/decode_splits_gqa.py: KV=1024 20.5 us unsplit vs 27.0 with 3 splits, 2048: 38.9 vs 45.2, 4096: 69.7 vs 72.2).
+        if (base * 10 >= slots * 8 || (base >= sm_count() && num_n_blocks <= 64)) {
             splits = 1;
         } else {
             const int max_splits = std::min({128, std::max(1, num_n_blocks / 4), num_n_blocks});
