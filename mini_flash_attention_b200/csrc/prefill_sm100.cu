@@ -658,15 +658,14 @@ template <typename T, int DPAD>
 static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                     const PrefillKParams& p, cudaStream_t stream) {
     using Cfg = PrefillCfg<DPAD>;
-    // exp2 placement.  A quarter of the exponentials on the FMA pipe (polynomial) is faster while the SM clock is high:
-    // +2 % at S=1024 (0.68 ms launches).  A launch of several ms runs into the board power cap (sw_power_cap,
-    // 1.59-1.68 GHz), where the extra FMA work costs more clock than the relieved MUFU gives: all-MUFU is +1.5 % at the
-    // headline S=4096 (9 ms) and +2-3 % causal (scripts/tune_prefill.py, r01g).  So: by the work of the launch.
-    // MFA_PREFILL_POLY=0/1 forces one form (tuning aid).
-    static const int poly_env = [] { const char* e = getenv("MFA_PREFILL_POLY"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
-    const double mflop = 4e-6 * (double)p.batch * p.heads * (double)p.seqlen_q * (double)p.seqlen_k * (double)DPAD *
-                         (p.has_hi ? 0.5 : 1.0);
-    const bool poly = poly_env >= 0 ? (poly_env == 1) : (mflop < 3.0e6);   // < ~3 TFLOP per launch (~3 ms)
+    // exp2 placement.  Default: every exponential on the MUFU.  The kernel can put a quarter of them on the FMA pipe
+    // (degree-3 polynomial, kPoly = true), which is 2 % faster for an ISOLATED launch on a cold, full-clock GPU (S=1024:
+    // 913 vs 894 TFLOP/s with a sync between launches) -- but any sustained stream of launches sits at the board power
+    // cap (sw_power_cap, 1.6-1.7 GHz), where the extra FMA work costs more clock than the relieved MUFU gives back:
+    // back-to-back loops of >= 200 ms measure MUFU-only +1.5-2 % non-causal and +4-6 % causal at S=1024 and S=2048,
+    // +1.7 % at the headline S=4096 (scripts/prefill_poly_ab.py, bench.py A/B on the same box).  Steady state is what a
+    // serving loop sees, so MUFU-only is the default; MFA_PREFILL_POLY=1 selects the polynomial form.
+    static const bool poly = [] { const char* e = getenv("MFA_PREFILL_POLY"); return e && e[0] == '1'; }();
     auto kern = poly ? prefill_fwd_kernel<T, DPAD, true> : prefill_fwd_kernel<T, DPAD, false>;
     static bool attr_done[64][2] = {};
     int dev = 0;

@@ -11,9 +11,7 @@ hides under the copies:
 
 The arithmetic is the unmodified public op (`_C.mini_flash_attention_forward` with `out=` into a staging buffer) on
 each chunk; chunks are whole batch elements, which are independent, so the result is bit-identical to the
-one-shot call whenever both run the same exp2 variant of the prefill kernel (the library picks MUFU-only for launches of
-more than ~3 TFLOP, prefill_sm100.cu launch_prefill_t; the two variants differ by fp32 rounding of a quarter of the
-exponentials, far inside the tolerance).  PyTorch supplies streams, events and pinned/device memory -- plumbing only.
+one-shot call.  PyTorch supplies streams, events and pinned/device memory -- plumbing only.
 """
 from __future__ import annotations
 
