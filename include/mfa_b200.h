@@ -177,7 +177,10 @@ int mfa_combine_partials(const float* packed, int num_partials, int rows, int he
  *   mfa_xchg_connect: handles = world x MFA_XCHG_HANDLE_BYTES bytes in rank order (cudaIpcOpenMemHandle per peer)
  *   mfa_xchg_connect_ptrs: the same with raw device pointers (ranks that live in ONE process; tests)
  *   mfa_xchg_local_ptr: the local buffer's device pointer (for mfa_xchg_connect_ptrs)
- *   mfa_xchg_status:  0, or 1 + the rank whose push did not arrive within the timeout (synchronises the device)
+ *   mfa_xchg_status:  0, or 1 + the rank whose push did not arrive within the timeout (synchronises the device).
+ *                     Sticky.  A row whose peers timed out is written as NaN (output and LSE), never as a partial sum.
+ *                     The timeout is ~2 s (MFA_XCHG_TIMEOUT_MS in the environment of mfa_xchg_create overrides it).
+ *   mfa_xchg_clear_status: returns the status like mfa_xchg_status and resets it to 0
  *   mfa_decode_kv_sharded_workspace_bytes: scratch for num_splits (>= 1) splits: splits * batch*heads * (D+1) floats */
 #define MFA_XCHG_HANDLE_BYTES 64
 #define MFA_XCHG_MAX_WORLD 8
@@ -188,6 +191,7 @@ int    mfa_xchg_connect(mfa_xchg_t* x, const void* handles);
 int    mfa_xchg_connect_ptrs(mfa_xchg_t* x, void* const* peer_ptrs);
 void*  mfa_xchg_local_ptr(mfa_xchg_t* x);
 int    mfa_xchg_status(mfa_xchg_t* x);
+int    mfa_xchg_clear_status(mfa_xchg_t* x);
 int    mfa_xchg_destroy(mfa_xchg_t* x);
 size_t mfa_decode_kv_sharded_workspace_bytes(const mfa_params_t* p, int num_splits);
 int    mfa_decode_fwd_kv_sharded(const mfa_params_t* p, void* workspace, size_t workspace_bytes, mfa_xchg_t* x,

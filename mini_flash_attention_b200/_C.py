@@ -46,7 +46,8 @@ def _tma_ok(t: torch.Tensor) -> bool:
     """TMA needs a 16-byte aligned base and 16-byte multiples for every non-innermost stride."""
     if t.data_ptr() % 16:
         return False
-    return all(s % 8 == 0 for s in t.stride()[:-1])
+    # a broadcast view (expand(): stride 0 on an extent > 1) cannot be expressed by a tensor map either
+    return all(s % 8 == 0 and (s > 0 or n <= 1) for s, n in zip(t.stride()[:-1], t.shape[:-1])) and t.stride(-1) == 1
 
 
 def _tma_ready(t: torch.Tensor) -> torch.Tensor:

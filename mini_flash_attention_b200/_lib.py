@@ -67,7 +67,7 @@ EXPORTS = (
     "mfa_decode_workspace_bytes", "mfa_decode_fwd", "mfa_combine_partials", "mfa_launch_count", "mfa_selftest_umma",
     "mfa_debug_set_trace", "mfa_selftest_umma2", "mfa_debug_set_prefill_impl", "mfa_kvcache_append",
     "mfa_xchg_create", "mfa_xchg_export", "mfa_xchg_connect", "mfa_xchg_connect_ptrs", "mfa_xchg_local_ptr",
-    "mfa_xchg_status", "mfa_xchg_destroy", "mfa_decode_kv_sharded_workspace_bytes", "mfa_decode_fwd_kv_sharded",
+    "mfa_xchg_status", "mfa_xchg_clear_status", "mfa_xchg_destroy", "mfa_decode_kv_sharded_workspace_bytes", "mfa_decode_fwd_kv_sharded",
 )
 XCHG_HANDLE_BYTES = 64
 XCHG_MAX_WORLD = 8
@@ -118,6 +118,8 @@ def load() -> ctypes.CDLL:
     lib.mfa_xchg_local_ptr.restype = ctypes.c_void_p
     lib.mfa_xchg_status.argtypes = [ctypes.c_void_p]
     lib.mfa_xchg_status.restype = ctypes.c_int
+    lib.mfa_xchg_clear_status.argtypes = [ctypes.c_void_p]
+    lib.mfa_xchg_clear_status.restype = ctypes.c_int
     lib.mfa_xchg_destroy.argtypes = [ctypes.c_void_p]
     lib.mfa_xchg_destroy.restype = ctypes.c_int
     lib.mfa_decode_kv_sharded_workspace_bytes.argtypes = [P, ctypes.c_int]

@@ -496,7 +496,14 @@ int mfa_xchg_create(int world, int rank, int max_rows, int head_dim, mfa_xchg_t*
     x->connected = false;
     int khz = 0;
     cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, x->device);
-    x->timeout_cycles = (long long)(khz > 0 ? khz : 2000000) * 1000LL * 2LL;   // ~2 s of SM clocks
+    // ~2 s of SM clocks by default (MFA_XCHG_TIMEOUT_MS overrides: a first call that loads modules on a peer, or a
+    // peer held in a debugger, may need more); on expiry the row is written as NaN and the status word is set
+    long long timeout_ms = 2000;
+    if (const char* e = getenv("MFA_XCHG_TIMEOUT_MS")) {
+        const long long v = atoll(e);
+        if (v > 0) timeout_ms = v;
+    }
+    x->timeout_cycles = (long long)(khz > 0 ? khz : 2000000) * timeout_ms;
     cudaError_t e = cudaMalloc(&x->local, x->bytes);
     if (e != cudaSuccess) {
         delete x;
@@ -563,6 +570,19 @@ int mfa_xchg_status(mfa_xchg_t* x) {
         return -1;
     }
     return (int)st;
+}
+
+int mfa_xchg_clear_status(mfa_xchg_t* x) {
+    const int st = mfa_xchg_status(x);
+    if (st > 0) {
+        const uint32_t zero = 0;
+        cudaError_t e = cudaMemcpy(static_cast<char*>(x->local) + x->data_bytes + x->flag_bytes, &zero, sizeof(zero), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            cuda_fail(e, "exchange status clear");
+            return -1;
+        }
+    }
+    return st;
 }
 
 int mfa_xchg_destroy(mfa_xchg_t* x) {

@@ -36,6 +36,24 @@
 #include "kparams.h"
 #include "ptx.cuh"
 
+// Register split of the 64 K registers of an SM over the CTA's 384 threads (setmaxnreg): 256 softmax threads and
+// 128 data-movement / MMA / allocator threads; 256 * SOFTMAX + 128 * HELPER <= 65536.
+#ifndef MFA_REG_SOFTMAX
+#define MFA_REG_SOFTMAX 216
+#endif
+#ifndef MFA_REG_HELPER
+#define MFA_REG_HELPER 72
+#endif
+// P hand-off from the softmax threads to the MMA warp.  MFA_PSPLIT 1: in two halves (p_lo after KV rows 0-63, p_hi after
+// 64-127) so that the first P.V k-steps run while the second half is exponentiated; 0: one hand-off per tile (one wait
+// and one tcgen05.wait::st / fence / arrive per thread less).  MFA_PARRIVE_WARP 1: one arrival per WARP (lane 0 after
+// __syncwarp; barrier count 4) instead of one per thread (count 128).
+#ifndef MFA_PSPLIT
+#define MFA_PSPLIT 1
+#endif
+#ifndef MFA_PARRIVE_WARP
+#define MFA_PARRIVE_WARP 0
+#endif
 #ifndef MFA_POLY_MASK
 #define MFA_POLY_MASK 0x8u   // pair 3 of every 4 -> a quarter of the exponentials off the MUFU (measured best)
 #endif
@@ -85,6 +103,16 @@ struct PrefillCfg {
 #define MFA_STAGES128 4
 #endif
     static constexpr int kStages = (DPAD == 64) ? 8 : (DPAD == 128 ? MFA_STAGES128 : 2);
+    // Flat K/V stream (kStages >= 4): the ring is used as kStages/2 DOUBLE SLOTS [V_j | K_{j+1}] with one full and one
+    // empty barrier each -- the two tiles one KV step of the MMA warp needs arrive under one barrier, and the stream
+    // runs across work items ([V_last(item a) | K_first(item a+1)]).  head_dim 256 has room for 2 slots only and keeps
+    // the per-tile ring.
+#ifdef MFA_NO_FLAT
+    static constexpr bool kFlat = false;   // tuning aid: the per-tile ring of round 1 at every head_dim
+#else
+    static constexpr bool kFlat = kStages >= 4;
+#endif
+    static constexpr int kDS = kStages / 2;
     static constexpr int kQBytes = kNQ * kQTileBytes;
     static constexpr int kRingBytes = kStages * kKVTileBytes;
     static constexpr int kBarOffset = kQBytes + kRingBytes;
@@ -107,6 +135,15 @@ __device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_addr, int kstep) {
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep) {
     const uint32_t addr = tile_addr + kstep * (16 * 128);
     return umma_smem_desc(addr, /*LBO*/ 128 * 128, /*SBO*/ 1024, /*SW128*/ 2);
+}
+
+// Opaque copy of a loop-invariant value.  The MMA warp lives on 72-80 registers; without this the compiler hoists every
+// `base + constant` TMEM / shared-memory address of the unrolled MMA batches out of the KV loop, spills them to local
+// memory and reloads them (LDL, ~40 cycles of exposed latency) in front of every batch of tcgen05.mma -- seen in the SASS
+// of the round-1 kernel.  Re-deriving them from one laundered base costs one uniform add each.
+__device__ __forceinline__ uint32_t opaque(uint32_t x) {
+    asm volatile("" : "+r"(x));
+    return x;
 }
 
 // 2^x for two packed floats, x <= ~8, on the FMA pipe: clamp, round-to-nearest split x = n + f (|f| <= 0.5) with
@@ -241,8 +278,8 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
         for (int i = 0; i < 2; ++i) {
             mbar_init(&q_full[i], 1);
             mbar_init(&s_full[i], 1);
-            mbar_init(&p_lo[i], 128);
-            mbar_init(&p_hi[i], 128);
+            mbar_init(&p_lo[i], MFA_PARRIVE_WARP ? 4 : 128);
+            mbar_init(&p_hi[i], MFA_PARRIVE_WARP ? 4 : 128);
             mbar_init(&o_full[i], 1);
             mbar_init(&q_empty[i], 1);
         }
@@ -266,7 +303,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
     // data-movement warpgroup hands most of its share to the two softmax warpgroups (whole S row in registers).
     // (Each setmaxnreg sits at the top of its own role branch so that ptxas sees the budget per region.)
     if (warp >= 8) {
-      asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MFA_REG_HELPER));
     if (warp == 8) {
         // ======================================================================= TMA producer
         // Warp-uniform control flow with one ELECTED lane issuing (see the MMA warp): under a divergent
@@ -276,51 +313,30 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             prefetch_tensormap(&tmK);
             prefetch_tensormap(&tmV);
         }
-        uint32_t tail_phase = 0;
-        int it = 0;          // K/V ring position, runs across items
-        uint32_t q_cnt = 0;  // valid items so far
-        for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-            const PrefillItem w = prefill_item<kNQ>(p, item);
-            if (!w.valid) continue;
-            const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
-            const int q_b_coord = p.cu_seqlens_q ? 0 : w.b;
-            // Q tiles of this item (both, also when a tile has no work: keeps the barrier phases uniform); the
-            // previous item's S MMAs must be done with the buffer
-#pragma unroll
-            for (int i = 0; i < kNQ; ++i) {
-                if (q_cnt > 0) mbar_wait(&q_empty[i], (q_cnt - 1) & 1);
-                if (elect_one()) {
-                    mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
-#pragma unroll
-                    for (int sb = 0; sb < Cfg::kSub; ++sb)
-                        tma_load_4d(q_smem + i * Cfg::kQTileBytes + sb * Cfg::kSubBytes, &tmQ, &q_full[i], sb * 64,
-                                    q_row_coord + i * kBM, w.h, q_b_coord);
-                }
-                __syncwarp();
-            }
-            ++q_cnt;
-            const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
-            const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
-            // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
-            // batches TMA's out-of-bounds fill does it; for packed / paged K/V the producer warp zeroes them.
-            const bool need_tail_fix = (bt != nullptr) || packed_k;
-            for (int j = w.j_lo; j < w.n_max; ++j) {
-                const int row0 = j * kBN;
-                const int rows_valid = min(w.len_k - row0, kBN);
-#pragma unroll 1
-                for (int kv = 0; kv < 2; ++kv, ++it) {
-                    const int s = it % kStages;
-                    const uint32_t ph = (it / kStages) & 1;
-                    const CUtensorMap* tm = kv ? &tmV : &tmK;
-                    uint8_t* dst = ring + s * Cfg::kKVTileBytes;
-                    const bool fix = kv && need_tail_fix && rows_valid < kBN;
-                    uint64_t* bar = fix ? tail_bar : &kv_full[s];
-                    mbar_wait(&kv_empty[s], ph ^ 1);
+        if constexpr (Cfg::kFlat) {
+            uint32_t tail_phase = 0;
+            uint32_t ds = 0;             // double-slot counter, runs across items
+            bool open = false;           // double slot `ds` holds a V tile (half A) and waits for the K tile that closes it
+            uint32_t q_ld[2] = {0, 0};   // loads of Q tile i so far (parity base of q_full / q_empty)
+            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+                const PrefillItem w = prefill_item<kNQ>(p, item);
+                if (!w.valid || w.n_max == 0) continue;   // nothing to load: the softmax warps write the zero rows alone
+                const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
+                const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
+                // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
+                // batches TMA's out-of-bounds fill does it; for packed / paged K/V the producer warp zeroes them.
+                const bool need_tail_fix = (bt != nullptr) || packed_k;
+                // one K or V tile of KV tile j into `dst`; its bytes are counted on `bar` (with the phase's one arrival
+                // when `arrive`, as a bare expect_tx otherwise)
+                auto load_tile = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* bar, bool arrive, int j) {
+                    const int row0 = j * kBN;
                     if (elect_one()) {
                         if (bt) {
+                            const int rows_valid = min(w.len_k - row0, kBN);
                             const int nchunks = (rows_valid + p.kv_box_rows - 1) / p.kv_box_rows;
                             const int chunk_bytes = p.kv_box_rows * 128;
-                            mbar_arrive_expect_tx(bar, (uint32_t)(nchunks * chunk_bytes * Cfg::kSub));
+                            const uint32_t bytes = (uint32_t)(nchunks * chunk_bytes * Cfg::kSub);
+                            if (arrive) mbar_arrive_expect_tx(bar, bytes); else mbar_expect_tx(bar, bytes);
                             for (int c = 0; c < nchunks; ++c) {
                                 const int row = row0 + c * p.kv_box_rows;
                                 const int pg = row / p.page;
@@ -328,30 +344,162 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                                 const int blk = bt[pg];
 #pragma unroll
                                 for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                    tma_load_4d(dst + sb * Cfg::kSubBytes + c * chunk_bytes, tm, bar, sb * 64, in_page,
-                                                w.kh, blk);
+                                    tma_load_4d(dst + sb * Cfg::kSubBytes + c * chunk_bytes, tm, bar, sb * 64, in_page, w.kh, blk);
                             }
                         } else {
-                            mbar_arrive_expect_tx(bar, Cfg::kKVTileBytes);
+                            if (arrive) mbar_arrive_expect_tx(bar, Cfg::kKVTileBytes); else mbar_expect_tx(bar, Cfg::kKVTileBytes);
 #pragma unroll
                             for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                tma_load_4d(dst + sb * Cfg::kSubBytes, tm, bar, sb * 64, (packed_k ? w.k_off : 0) + row0,
-                                            w.kh, packed_k ? 0 : w.b);
+                                tma_load_4d(dst + sb * Cfg::kSubBytes, tm, bar, sb * 64, (packed_k ? w.k_off : 0) + row0, w.kh,
+                                            packed_k ? 0 : w.b);
                         }
                     }
                     __syncwarp();
-                    if (fix) {
-                        // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
-                        mbar_wait(tail_bar, tail_phase);
-                        tail_phase ^= 1;
-                        for (int r = rows_valid; r < kBN; ++r) {
+                };
+                const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
+                const int q_b_coord = p.cu_seqlens_q ? 0 : w.b;
+                for (int j = w.j_lo; j < w.n_max; ++j) {
+                    // ---- K_j: half B of the open double slot (closing it), or of a fresh one at the very start
+                    {
+                        const uint32_t st = ds % Cfg::kDS;
+                        if (!open) mbar_wait(&kv_empty[st], ((ds / Cfg::kDS) & 1) ^ 1);
+                        load_tile(&tmK, ring + (2 * st + 1) * Cfg::kKVTileBytes, &kv_full[st], true, j);
+                        ++ds;
+                        open = false;
+                    }
+                    if (j == w.j_lo) {
+                        // Q tiles of this item, AFTER its first K tile (that one closes the previous item's last double
+                        // slot, which must not wait for the Q buffers).  Only tiles with KV work are loaded: a tile
+                        // without work is never read by an MMA, and a bulk copy nobody awaits could land after the CTA
+                        // exited or be re-armed before it landed.  q_full / q_empty phases count LOADS of tile i; the
+                        // MMA warp commits q_empty[i] right after the tile's last S MMA, about one KV step before the
+                        // item ends, so this wait is normally over when the producer gets here.
 #pragma unroll
-                            for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                *reinterpret_cast<uint32_t*>(dst + sb * Cfg::kSubBytes + r * 128 + lane * 4) = 0u;
+                        for (int i = 0; i < kNQ; ++i) {
+                            if (w.n_i[i] == 0) continue;
+                            if (q_ld[i] > 0) mbar_wait(&q_empty[i], (q_ld[i] - 1) & 1);
+                            if (elect_one()) {
+                                mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
+#pragma unroll
+                                for (int sb = 0; sb < Cfg::kSub; ++sb)
+                                    tma_load_4d(q_smem + i * Cfg::kQTileBytes + sb * Cfg::kSubBytes, &tmQ, &q_full[i], sb * 64,
+                                                q_row_coord + i * kBM, w.h, q_b_coord);
+                            }
+                            __syncwarp();
+                            ++q_ld[i];
                         }
-                        fence_proxy_async_smem();
+                    }
+                    // ---- V_j: half A of the next double slot, left open
+                    {
+                        const uint32_t st = ds % Cfg::kDS;
+                        mbar_wait(&kv_empty[st], ((ds / Cfg::kDS) & 1) ^ 1);
+                        uint8_t* dst = ring + (2 * st) * Cfg::kKVTileBytes;
+                        const int rows_valid = min(w.len_k - j * kBN, kBN);
+                        const bool fix = need_tail_fix && rows_valid < kBN;
+                        load_tile(&tmV, dst, fix ? tail_bar : &kv_full[st], fix, j);
+                        if (fix) {
+                            // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
+                            // (the arrival that closes this double slot -- the next K tile or the final arrive -- follows)
+                            mbar_wait(tail_bar, tail_phase);
+                            tail_phase ^= 1;
+                            for (int r = rows_valid; r < kBN; ++r) {
+#pragma unroll
+                                for (int sb = 0; sb < Cfg::kSub; ++sb)
+                                    *reinterpret_cast<uint32_t*>(dst + sb * Cfg::kSubBytes + r * 128 + lane * 4) = 0u;
+                            }
+                            fence_proxy_async_smem();
+                            __syncwarp();
+                        }
+                        open = true;
+                    }
+                }
+            }
+            if (open) {   // the CTA's last V tile: nothing follows, close its double slot
+                if (elect_one()) mbar_arrive(&kv_full[ds % Cfg::kDS]);
+                __syncwarp();
+            }
+        } else {
+            uint32_t tail_phase = 0;
+            int it = 0;                  // K/V ring position, runs across items
+            uint32_t q_ld[2] = {0, 0};   // loads of Q tile i so far (parity base of q_full / q_empty)
+            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+                const PrefillItem w = prefill_item<kNQ>(p, item);
+                if (!w.valid) continue;
+                const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
+                const int q_b_coord = p.cu_seqlens_q ? 0 : w.b;
+                // Q tiles of this item -- only the tiles that have KV work (n_i > 0).  A tile without work is never read by
+                // an MMA, so loading it would leave a bulk copy in flight that nobody awaits (it could land after the CTA
+                // exited, or be re-armed before it landed).  q_full / q_empty phases therefore count LOADS of tile i
+                // (q_ld[i]), not items: every load is awaited by the MMA warp before it commits q_empty, and the producer
+                // observes that commit before the next load, so neither barrier ever runs more than one phase ahead.
+    #pragma unroll
+                for (int i = 0; i < kNQ; ++i) {
+                    if (w.n_i[i] == 0) continue;
+                    if (q_ld[i] > 0) mbar_wait(&q_empty[i], (q_ld[i] - 1) & 1);
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
+    #pragma unroll
+                        for (int sb = 0; sb < Cfg::kSub; ++sb)
+                            tma_load_4d(q_smem + i * Cfg::kQTileBytes + sb * Cfg::kSubBytes, &tmQ, &q_full[i], sb * 64,
+                                        q_row_coord + i * kBM, w.h, q_b_coord);
+                    }
+                    __syncwarp();
+                    ++q_ld[i];
+                }
+                const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
+                const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
+                // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
+                // batches TMA's out-of-bounds fill does it; for packed / paged K/V the producer warp zeroes them.
+                const bool need_tail_fix = (bt != nullptr) || packed_k;
+                for (int j = w.j_lo; j < w.n_max; ++j) {
+                    const int row0 = j * kBN;
+                    const int rows_valid = min(w.len_k - row0, kBN);
+    #pragma unroll 1
+                    for (int kv = 0; kv < 2; ++kv, ++it) {
+                        const int s = it % kStages;
+                        const uint32_t ph = (it / kStages) & 1;
+                        const CUtensorMap* tm = kv ? &tmV : &tmK;
+                        uint8_t* dst = ring + s * Cfg::kKVTileBytes;
+                        const bool fix = kv && need_tail_fix && rows_valid < kBN;
+                        uint64_t* bar = fix ? tail_bar : &kv_full[s];
+                        mbar_wait(&kv_empty[s], ph ^ 1);
+                        if (elect_one()) {
+                            if (bt) {
+                                const int nchunks = (rows_valid + p.kv_box_rows - 1) / p.kv_box_rows;
+                                const int chunk_bytes = p.kv_box_rows * 128;
+                                mbar_arrive_expect_tx(bar, (uint32_t)(nchunks * chunk_bytes * Cfg::kSub));
+                                for (int c = 0; c < nchunks; ++c) {
+                                    const int row = row0 + c * p.kv_box_rows;
+                                    const int pg = row / p.page;
+                                    const int in_page = row - pg * p.page;
+                                    const int blk = bt[pg];
+    #pragma unroll
+                                    for (int sb = 0; sb < Cfg::kSub; ++sb)
+                                        tma_load_4d(dst + sb * Cfg::kSubBytes + c * chunk_bytes, tm, bar, sb * 64, in_page,
+                                                    w.kh, blk);
+                                }
+                            } else {
+                                mbar_arrive_expect_tx(bar, Cfg::kKVTileBytes);
+    #pragma unroll
+                                for (int sb = 0; sb < Cfg::kSub; ++sb)
+                                    tma_load_4d(dst + sb * Cfg::kSubBytes, tm, bar, sb * 64, (packed_k ? w.k_off : 0) + row0,
+                                                w.kh, packed_k ? 0 : w.b);
+                            }
+                        }
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(&kv_full[s]);
+                        if (fix) {
+                            // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
+                            mbar_wait(tail_bar, tail_phase);
+                            tail_phase ^= 1;
+                            for (int r = rows_valid; r < kBN; ++r) {
+    #pragma unroll
+                                for (int sb = 0; sb < Cfg::kSub; ++sb)
+                                    *reinterpret_cast<uint32_t*>(dst + sb * Cfg::kSubBytes + r * 128 + lane * 4) = 0u;
+                            }
+                            fence_proxy_async_smem();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&kv_full[s]);
+                        }
                     }
                 }
             }
@@ -370,11 +518,12 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
 
             auto issue_S = [&](int i, int stage) {
                 if (elect_one()) {
-                    const uint32_t qa = q_addr + i * Cfg::kQTileBytes;
-                    const uint32_t ka = ring_addr + stage * Cfg::kKVTileBytes;
+                    const uint32_t qa = opaque(q_addr) + i * Cfg::kQTileBytes;
+                    const uint32_t ka = opaque(ring_addr) + stage * Cfg::kKVTileBytes;
+                    const uint32_t tb = opaque(tmem_base);
 #pragma unroll
                     for (int ks = 0; ks < DPAD / 16; ++ks)
-                        umma_ss(tmem_base + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
+                        umma_ss(tb + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
                                 ks > 0 ? 1u : 0u);
                     umma_commit(&s_full[i]);
                 }
@@ -382,10 +531,22 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             };
             auto issue_PV = [&](int i, int stage, bool accumulate, int ks0, int ks1, bool commit_o) {
                 if (elect_one()) {
-                    const uint32_t va = ring_addr + stage * Cfg::kKVTileBytes;
+                    const uint32_t va = opaque(ring_addr) + stage * Cfg::kKVTileBytes;
+                    const uint32_t tb = opaque(tmem_base);
 #pragma unroll
                     for (int ks = ks0; ks < ks1; ++ks)
-                        umma_ts(tmem_base + Cfg::kTmemO + i * DPAD, tmem_base + Cfg::kTmemS + i * 128 + ks * 8,
+                        umma_ts(tb + Cfg::kTmemO + i * DPAD, tb + Cfg::kTmemS + i * 128 + ks * 8,
+                                desc_mnmajor(va, ks), idescO, (accumulate || ks > 0) ? 1u : 0u);
+                    if (commit_o) umma_commit(&o_full[i]);
+                }
+                __syncwarp();
+            };
+            auto issue_PV_at = [&](int i, uint32_t va, bool accumulate, int ks0, int ks1, bool commit_o) {
+                if (elect_one()) {
+                    const uint32_t tb = opaque(tmem_base);
+#pragma unroll
+                    for (int ks = ks0; ks < ks1; ++ks)
+                        umma_ts(tb + Cfg::kTmemO + i * DPAD, tb + Cfg::kTmemS + i * 128 + ks * 8,
                                 desc_mnmajor(va, ks), idescO, (accumulate || ks > 0) ? 1u : 0u);
                     if (commit_o) umma_commit(&o_full[i]);
                 }
@@ -407,75 +568,190 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             // without an issue token, P.V + S as one 16-MMA batch (one wait per tile), early non-blocking probes
             // (test_wait: ptxas consumes the predicate at once, the latency stays exposed), splitting the softmax of
             // a tile by key columns over both warpgroups.
-            int it = 0;                   // K/V ring position, runs across items
-            uint32_t q_cnt = 0;           // valid items so far
-            uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
-            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-                const PrefillItem w = prefill_item<kNQ>(p, item);
-                if (!w.valid) continue;
-#ifdef MFA_TRACE
-                tr_on = tr_cta && item == (int)blockIdx.x;
-#endif
-                const int n_max = w.n_max;
+            if constexpr (Cfg::kFlat) {
+                // FLAT STREAM.  The CTA's KV steps form one sequence across its work items.  Step (item, j) waits for
+                // ONE double slot [V_j | K_next] -- K_next is K_{j+1} of the item, or the first K tile of the next work
+                // item when j is the item's last -- issues P.V(j) and S(next) for both Q tiles and releases the slot with
+                // ONE commit: 5 barrier waits per step instead of 7, and the first S MMAs of item n+1 are in the queue
+                // before the last P.V of item n has finished (no drain at the item boundary; with the causal mask the
+                // lone last step of Q tile 1 overlaps the next item's first step of Q tile 0).
+                uint32_t ds = 0;              // double-slot counter, runs across items
+                uint32_t q_ld[2] = {0, 0};    // loads of Q tile i so far (the producer loads a tile only when it has KV work)
+                uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
+                // S_i(jn) of item wx from the K tile at `ka`: the tile's first S waits for its Q load, its last S
+                // releases the Q buffer (so the next item's Q is loaded about one KV step before it is needed)
+                auto s_step = [&](const PrefillItem& wx, int i, int jn, uint32_t ka) {
+                    if (wx.active(i, jn)) {
+                        if (jn == wx.lo_i[i]) {
+                            mbar_wait(&q_full[i], q_ld[i] & 1);
+                            tc_fence_after();
+                        }
+                        if (elect_one()) {
+                            const uint32_t qa = opaque(q_addr) + i * Cfg::kQTileBytes;
+                            const uint32_t tb = opaque(tmem_base);
 #pragma unroll
-                for (int i = 0; i < kNQ; ++i)
-                    if (w.n_i[i] > 0) mbar_wait(&q_full[i], q_cnt & 1);
-                if (n_max > 0) {
-                    const int sK = it % kStages;
-                    mbar_wait(&kv_full[sK], (it / kStages) & 1);
-                    ++it;
+                            for (int ks = 0; ks < DPAD / 16; ++ks)
+                                umma_ss(tb + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
+                                        ks > 0 ? 1u : 0u);
+                            umma_commit(&s_full[i]);
+                            if (jn == wx.n_i[i] - 1) umma_commit(&q_empty[i]);
+                        }
+                        __syncwarp();
+                        if (jn == wx.n_i[i] - 1) ++q_ld[i];
+                    }
+                };
+                auto next_work = [&](int item, PrefillItem& wx) -> int {
+                    for (; item < total_items; item += gridDim.x) {
+                        wx = prefill_item<kNQ>(p, item);
+                        if (wx.valid && wx.n_max > 0) return item;
+                    }
+                    return -1;
+                };
+                PrefillItem w;
+                int item = next_work(blockIdx.x, w);
+                if (item >= 0) {
+                    // the CTA's first double slot holds only K_first
+                    mbar_wait(&kv_full[0], 0);
                     tc_fence_after();
 #pragma unroll
-                    for (int i = 0; i < kNQ; ++i)
-                        if (w.active(i, w.j_lo)) issue_S(i, sK);
-                    commit(&kv_empty[sK]);
+                    for (int i = 0; i < kNQ; ++i) s_step(w, i, w.j_lo, ring_addr + Cfg::kKVTileBytes);
+                    commit(&kv_empty[0]);
+                    ds = 1;
                 }
-                for (int j = w.j_lo; j < n_max; ++j) {
-                    const int sV = it % kStages;
-                    mbar_wait(&kv_full[sV], (it / kStages) & 1);
-                    ++it;
-                    const bool has_next = (j + 1 < n_max);
-                    int sK = 0;
-                    if (has_next) {
-                        sK = it % kStages;
+                while (item >= 0) {
+#ifdef MFA_TRACE
+                    tr_on = tr_cta && item == (int)blockIdx.x;
+#endif
+                    PrefillItem wn;
+                    int nitem = -1;
+                    for (int j = w.j_lo; j < w.n_max; ++j) {
+                        const bool last = (j + 1 == w.n_max);
+                        if (last) nitem = next_work(item + (int)gridDim.x, wn);
+                        const uint32_t st = ds % Cfg::kDS;
+                        mbar_wait(&kv_full[st], (ds / Cfg::kDS) & 1);
+                        ++ds;
+                        tc_fence_after();
+                        MFA_TR(2, j, 0);
+                        const uint32_t va = opaque(ring_addr) + (2 * st) * Cfg::kKVTileBytes;
+                        const uint32_t ka = va + Cfg::kKVTileBytes;
+#pragma unroll
+                        for (int i = 0; i < kNQ; ++i) {
+                            if (w.active(i, j)) {
+                                const uint32_t par = (t_cnt[i] + (uint32_t)(j - w.lo_i[i])) & 1u;
+                                // (the first P.V of an item overwrites O_i: safe, because every softmax thread finished
+                                // the previous item's epilogue -- its TMEM reads of O_i included -- before it released this P)
+#if MFA_PSPLIT
+                                mbar_wait(&p_lo[i], par);
+                                tc_fence_after();
+                                MFA_TR(2, j, 1 + 3 * i);
+                                issue_PV_at(i, va, j > w.lo_i[i], 0, kBN / 32, false);
+                                mbar_wait(&p_hi[i], par);
+                                tc_fence_after();
+                                MFA_TR(2, j, 2 + 3 * i);
+                                issue_PV_at(i, va, j > w.lo_i[i], kBN / 32, kBN / 16, true);
+#else
+                                mbar_wait(&p_hi[i], par);
+                                tc_fence_after();
+                                MFA_TR(2, j, 2 + 3 * i);
+                                issue_PV_at(i, va, j > w.lo_i[i], 0, kBN / 16, true);
+#endif
+                            }
+                            if (!last) s_step(w, i, j + 1, ka);
+                            MFA_TR(2, j, 3 + 3 * i);
+                        }
+                        // the item's last step: both P.V first, then the next item's first S (its Q tiles may still be
+                        // in flight; the wait must not hold back this item's P.V)
+                        if (last && nitem >= 0) {
+#pragma unroll
+                            for (int i = 0; i < kNQ; ++i) s_step(wn, i, wn.j_lo, ka);
+                        }
+                        commit(&kv_empty[st]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < kNQ; ++i) t_cnt[i] += (uint32_t)w.count(i);
+                    w = wn;
+                    item = nitem;
+                }
+            } else {
+                int it = 0;                   // K/V ring position, runs across items
+                uint32_t q_ld[2] = {0, 0};    // loads of Q tile i so far (the producer loads a tile only when it has KV work)
+                uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
+                for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+                    const PrefillItem w = prefill_item<kNQ>(p, item);
+                    if (!w.valid) continue;
+    #ifdef MFA_TRACE
+                    tr_on = tr_cta && item == (int)blockIdx.x;
+    #endif
+                    const int n_max = w.n_max;
+    #pragma unroll
+                    for (int i = 0; i < kNQ; ++i)
+                        if (w.n_i[i] > 0) mbar_wait(&q_full[i], q_ld[i] & 1);
+                    if (n_max > 0) {
+                        const int sK = it % kStages;
                         mbar_wait(&kv_full[sK], (it / kStages) & 1);
                         ++it;
+                        tc_fence_after();
+    #pragma unroll
+                        for (int i = 0; i < kNQ; ++i)
+                            if (w.active(i, w.j_lo)) issue_S(i, sK);
+                        commit(&kv_empty[sK]);
                     }
-                    tc_fence_after();
-                    MFA_TR(2, j, 0);
-#pragma unroll
-                    for (int i = 0; i < kNQ; ++i) {
-                        if (w.active(i, j)) {
-                            const uint32_t par = (t_cnt[i] + (uint32_t)(j - w.lo_i[i])) & 1u;
-                            // (the first P.V of an item overwrites O_i: safe, because every softmax thread finished the
-                            // previous item's epilogue -- its TMEM reads of O_i included -- before it released this P)
-                            mbar_wait(&p_lo[i], par);
-                            tc_fence_after();
-                            MFA_TR(2, j, 1 + 3 * i);
-                            issue_PV(i, sV, j > w.lo_i[i], 0, kBN / 32, false);
-                            mbar_wait(&p_hi[i], par);
-                            tc_fence_after();
-                            MFA_TR(2, j, 2 + 3 * i);
-                            issue_PV(i, sV, j > w.lo_i[i], kBN / 32, kBN / 16, true);
+                    for (int j = w.j_lo; j < n_max; ++j) {
+                        const int sV = it % kStages;
+                        mbar_wait(&kv_full[sV], (it / kStages) & 1);
+                        ++it;
+                        const bool has_next = (j + 1 < n_max);
+                        int sK = 0;
+                        if (has_next) {
+                            sK = it % kStages;
+                            mbar_wait(&kv_full[sK], (it / kStages) & 1);
+                            ++it;
                         }
-                        if (w.active(i, j + 1)) issue_S(i, sK);
-                        MFA_TR(2, j, 3 + 3 * i);
+                        tc_fence_after();
+                        MFA_TR(2, j, 0);
+    #pragma unroll
+                        for (int i = 0; i < kNQ; ++i) {
+                            if (w.active(i, j)) {
+                                const uint32_t par = (t_cnt[i] + (uint32_t)(j - w.lo_i[i])) & 1u;
+                                // (the first P.V of an item overwrites O_i: safe, because every softmax thread finished the
+                                // previous item's epilogue -- its TMEM reads of O_i included -- before it released this P)
+#if MFA_PSPLIT
+                                mbar_wait(&p_lo[i], par);
+                                tc_fence_after();
+                                MFA_TR(2, j, 1 + 3 * i);
+                                issue_PV(i, sV, j > w.lo_i[i], 0, kBN / 32, false);
+                                mbar_wait(&p_hi[i], par);
+                                tc_fence_after();
+                                MFA_TR(2, j, 2 + 3 * i);
+                                issue_PV(i, sV, j > w.lo_i[i], kBN / 32, kBN / 16, true);
+#else
+                                mbar_wait(&p_hi[i], par);
+                                tc_fence_after();
+                                MFA_TR(2, j, 2 + 3 * i);
+                                issue_PV(i, sV, j > w.lo_i[i], 0, kBN / 16, true);
+#endif
+                            }
+                            if (w.active(i, j + 1)) issue_S(i, sK);
+                            MFA_TR(2, j, 3 + 3 * i);
+                        }
+                        commit(&kv_empty[sV]);
+                        if (has_next) commit(&kv_empty[sK]);
                     }
-                    commit(&kv_empty[sV]);
-                    if (has_next) commit(&kv_empty[sK]);
+                    // every MMA that reads this item's Q tiles has been issued: release them to the producer
+    #pragma unroll
+                    for (int i = 0; i < kNQ; ++i) {
+                        if (w.n_i[i] > 0) {
+                            commit(&q_empty[i]);
+                            ++q_ld[i];
+                        }
+                        t_cnt[i] += (uint32_t)w.count(i);
+                    }
                 }
-                // every MMA that reads this item's Q tiles has been issued: release them to the producer
-#pragma unroll
-                for (int i = 0; i < kNQ; ++i) {
-                    commit(&q_empty[i]);
-                    t_cnt[i] += (uint32_t)w.count(i);
-                }
-                ++q_cnt;
             }
         }
     }
     } else {
-      asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+      asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MFA_REG_SOFTMAX));
       if (warp < 4 * kNQ) {
         // ======================================================================= softmax warpgroups
         const int i = warp >> 2;
@@ -587,9 +863,16 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                         pk[c] = Elem<T>::pack(p0, p1);
                     }
                     tmem_st32(tS + hf * 32, pk);
-                    tmem_wait_st();
-                    tc_fence_before();
-                    mbar_arrive(hf == 0 ? &p_lo[i] : &p_hi[i]);
+                    if (MFA_PSPLIT || hf == 1) {
+                        tmem_wait_st();
+                        tc_fence_before();
+#if MFA_PARRIVE_WARP
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(hf == 0 ? &p_lo[i] : &p_hi[i]);
+#else
+                        mbar_arrive(hf == 0 ? &p_lo[i] : &p_hi[i]);
+#endif
+                    }
                     MFA_TR(i, j, 4 + hf);
                 }
                 float sa, sb, sc, sd;

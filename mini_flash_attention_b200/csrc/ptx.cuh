@@ -49,6 +49,11 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
 }
+// raise the pending transaction count without arriving: lets two TMA loads that are issued at different times complete
+// ONE phase (the second one arrives with mbar_arrive_expect_tx, or a plain mbar_arrive closes the phase)
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
@@ -75,6 +80,10 @@ __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
 }
 // Wait until the phase with the given parity has completed.  The watchdog clock (%globaltimer, a slow shared
 // resource) is only read every 4096 failed polls, so that spinning warps do not slow the rest of the SM down.
+// On expiry the kernel TRAPS (the launch fails with an error instead of hanging the box).  -DMFA_WATCHDOG_PRINTF also
+// prints which barrier was stuck -- off by default: a printf call site makes every value that is live across it
+// (TMEM base, shared-memory bases, counters) a spill candidate, and in the 72-register MMA-issuing warp of the prefill
+// kernel those spills sat as LDLs in front of every batch of tcgen05.mma (round-1 SASS).
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     uint32_t spins = 0;
@@ -85,8 +94,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
             if (t0 == 0) {
                 t0 = t;
             } else if (t - t0 > MFA_WATCHDOG_NS) {
+#ifdef MFA_WATCHDOG_PRINTF
                 printf("mfa: mbarrier watchdog block(%d,%d,%d) thread %d bar@%u parity %u\n", blockIdx.x, blockIdx.y,
                        blockIdx.z, threadIdx.x, smem_u32(bar), parity);
+#endif
                 __trap();
             }
         }

@@ -38,10 +38,14 @@ const char* encode_tmap_4d(CUtensorMap* out, const void* base, bool is_bf16, con
     }
     for (int i = 1; i < 4; ++i) {
         int64_t s = strides_elems[i];
-        if (s <= 0 || dims[i] <= 1) {
-            // size-1 (or degenerate) dimension: any legal stride works; use the extent below it
+        if (dims[i] <= 1) {
+            // size-1 dimension: its stride is never applied, any legal value works; use the extent below it
             s = (i == 1) ? static_cast<int64_t>(gdim[0]) : static_cast<int64_t>(gstride[i - 2] / 2 * gdim[i - 1]);
             if (s % 8) s = (s + 7) / 8 * 8;
+        } else if (s <= 0) {
+            // a broadcast (expand()ed, stride 0) or reversed dimension of extent > 1: a tensor map cannot express it,
+            // and inventing a stride would read the wrong rows -- the caller must materialise the tensor
+            return "zero or negative stride on a dimension of extent > 1 (broadcast view): make the tensor contiguous";
         }
         if ((s * 2) % 16) return "tensor strides must be multiples of 16 bytes for TMA";
         gstride[i - 1] = static_cast<cuuint64_t>(s) * 2;

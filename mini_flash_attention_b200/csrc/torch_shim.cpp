@@ -38,9 +38,10 @@ void check_qkv(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v) {
 // TMA needs a 16-byte aligned base and 16-byte multiples for every non-innermost stride
 bool tma_ok(const at::Tensor& t) {
     if (reinterpret_cast<uintptr_t>(t.data_ptr()) % 16) return false;
+    // (a broadcast view -- expand(): stride 0 on an extent > 1 -- cannot be expressed by a tensor map either)
     for (int64_t d = 0; d + 1 < t.dim(); ++d)
-        if (t.stride(d) % 8) return false;
-    return true;
+        if (t.stride(d) % 8 || (t.stride(d) <= 0 && t.size(d) > 1)) return false;
+    return t.dim() == 0 || t.stride(t.dim() - 1) == 1;
 }
 at::Tensor tma_ready(const at::Tensor& t) { return tma_ok(t) ? t : t.contiguous(); }
 

@@ -94,19 +94,27 @@ __global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_
         st_release_sys(p.peer_flags[lane] + (int64_t)p.rank * p.max_rows + row, epoch);
     }
 
-    // ---- 3. wait for the R pushes of this row into the local buffer
+    // ---- 3. wait for the R pushes of this row into the local buffer.  The first polls are back to back (a peer that
+    // runs in step arrives within a few microseconds: an NVLink round trip); only a late peer is waited for with
+    // __nanosleep between polls.  A peer that never arrives within the timeout must not turn into silently wrong
+    // attention: the row is written as NaN (output and LSE) and the sticky status word names the missing rank.
+    bool timed_out = false;
     if (lane < p.world) {
         const uint32_t* f = p.peer_flags[p.rank] + (int64_t)lane * p.max_rows + row;
         const long long t0 = clock64();
+        int polls = 0;
         while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
-            if (clock64() - t0 > p.timeout_cycles) {
-                atomicExch(p.ctrs, 1u + (uint32_t)lane);   // a peer never arrived: reported by mfa_xchg_status()
-                break;
+            if (++polls > 128) {
+                if (clock64() - t0 > p.timeout_cycles) {
+                    atomicExch(p.ctrs, 1u + (uint32_t)lane);   // reported (and cleared) through mfa_xchg_status / _clear_status
+                    timed_out = true;
+                    break;
+                }
+                __nanosleep(32);
             }
-            __nanosleep(64);
         }
     }
-    __syncwarp();
+    timed_out = __any_sync(0xffffffffu, timed_out);
     __threadfence_system();
 
     // ---- 4. merge the R partial rows (L2 loads: the lines were written by peers, never trust L1)
@@ -139,6 +147,10 @@ __global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_
             }
         }
     }
+    if (timed_out) {   // visible in the data, not only in the status word
+        const float qnan = __int_as_float(0x7fc00000);
+        acc[0] = acc[1] = make_float4(qnan, qnan, qnan, qnan);
+    }
     T* out = static_cast<T*>(p.out) + (int64_t)(row / p.heads) * p.out_batch_stride + (int64_t)(row % p.heads) * p.out_head_stride;
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
@@ -150,7 +162,7 @@ __global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_
             *reinterpret_cast<uint2*>(out + col) = pk;
         }
     }
-    if (lane == 0 && p.lse_out) p.lse_out[row] = glse;
+    if (lane == 0 && p.lse_out) p.lse_out[row] = timed_out ? __int_as_float(0x7fc00000) : glse;
 
     // ---- 5. the last row of the grid closes the step: every CTA has read the epoch before it got here
     __syncwarp();

@@ -161,6 +161,7 @@ class KVShardExchange:
         from . import _lib
         self._lib = _lib.load()
         self.world, self.rank, self.max_rows, self.head_dim = world, rank, max_rows, head_dim
+        self.verify_steps, self._steps = 2, 0   # decode_kv_sharded checks the timeout status on the first calls
         h = ctypes.c_void_p()
         _lib.check(self._lib.mfa_xchg_create(world, rank, max_rows, head_dim, ctypes.byref(h)), "mfa_xchg_create")
         self.handle = h.value
@@ -181,13 +182,23 @@ class KVShardExchange:
         xs = [cls(world, r, max_rows, head_dim, _connect=False) for r in range(world)]
         ptrs = (ctypes.c_void_p * world)(*[x._lib.mfa_xchg_local_ptr(x.handle) for x in xs])
         for x in xs:
+            x.verify_steps = 0   # the ranks are streams of ONE host thread: a status read (device sync) between their launches would deadlock
             if world > 1:
                 _lib.check(x._lib.mfa_xchg_connect_ptrs(x.handle, ptrs), "mfa_xchg_connect_ptrs")
         return xs
 
-    def status(self) -> int:
-        """0, or 1 + the rank whose push did not arrive within the kernel's ~2 s timeout (synchronises the device)."""
-        return int(self._lib.mfa_xchg_status(self.handle))
+    def status(self, clear: bool = False) -> int:
+        """0, or 1 + the rank whose push did not arrive within the kernel's timeout (~2 s; MFA_XCHG_TIMEOUT_MS).
+        Synchronises the device.  Sticky until read with clear=True.  Rows that timed out are NaN in the output."""
+        fn = self._lib.mfa_xchg_clear_status if clear else self._lib.mfa_xchg_status
+        return int(fn(self.handle))
+
+    def check(self) -> None:
+        """Raise if any step since the last check timed out waiting for a peer (synchronises the device)."""
+        st = self.status(clear=True)
+        if st:
+            raise RuntimeError(f"KV-shard exchange: the push of rank {st - 1} did not arrive within the timeout "
+                               f"(rank {self.rank} of {self.world}); the affected output rows are NaN")
 
     def close(self) -> None:
         if getattr(self, "handle", None):
@@ -216,8 +227,15 @@ def decode_kv_sharded(q: torch.Tensor, k_cache_local: torch.Tensor, v_cache_loca
         from . import _C
         if exchange.world != world:
             raise ValueError("exchange was built for another world size")
-        return _C.decode_kv_sharded_fused(q, k_cache_local, v_cache_local, local_seqlens, block_table_local, num_splits,
-                                          exchange.handle)
+        out = _C.decode_kv_sharded_fused(q, k_cache_local, v_cache_local, local_seqlens, block_table_local, num_splits,
+                                         exchange.handle)
+        # Contract: a peer that does not arrive within the timeout leaves NaN rows and a sticky status word.  The first
+        # `verify_steps` calls (module loads, late ranks: the risky ones) check it here, at the cost of a device
+        # synchronisation; afterwards the caller polls exchange.check() at its own pace (never inside a graph capture).
+        if exchange._steps < exchange.verify_steps and not torch.cuda.is_current_stream_capturing():
+            exchange.check()
+        exchange._steps += 1
+        return out
     if partial_fn is None or combine_fn is None:
         from . import _C
         partial_fn = partial_fn or _C.decode_partial

@@ -78,6 +78,7 @@ def latency(fn, steps, warmup, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--parity-only", action="store_true", help="sections 1 and 2 only (tests/test_multigpu.py)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -147,6 +148,11 @@ def main():
                 "ok": bool(float(perr) <= tol)})
     assert float(perr) <= tol, float(perr)
 
+    if args.parity_only:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     # ------------------------------------------------------------------ 3. timings
     Bl, Hq, Hkv, page = 1, 32, 8, 256
     kv_list = [131072] if args.quick else [131072, 262144, 524288, 1048576]

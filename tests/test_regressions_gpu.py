@@ -1,0 +1,157 @@
+"""Regression tests for defects found in review:
+
+* broadcast views (expand(): stride 0 on an extent > 1) of q / k / v / the cache must give the same result as their
+  materialised copies -- a tensor map cannot express a zero stride, the host side has to materialise them (tmap.cu);
+* work items WITHOUT any KV work on the PERSISTENT grid (bottom-right causal with Sq >> Sk, windows past the end of K):
+  the Q tiles of such items are not loaded, and the barrier phases of the items around them stay in step;
+* the fused KV-shard exchange writes NaN, not a partial sum, for a row whose peer never arrived.
+"""
+import pytest
+import torch
+
+from conftest import TOL
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mfa(mfa_lib):
+    import mini_flash_attention
+    return mini_flash_attention
+
+
+def _r(shape, dt=torch.float16, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return torch.randn(*shape, device="cuda", dtype=dt, generator=g)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_prefill_broadcast_views(mfa, causal):
+    B, S, H, Hkv, D = 3, 300, 8, 2, 128
+    q = _r((B, S, H, D), seed=1)
+    k1, v1 = _r((1, S, Hkv, D), seed=2), _r((1, S, Hkv, D), seed=3)
+    k, v = k1.expand(B, S, Hkv, D), v1.expand(B, S, Hkv, D)          # batch stride 0
+    assert k.stride(0) == 0
+    want = mfa.flash_attn_func(q, k.contiguous(), v.contiguous(), causal=causal)
+    assert torch.equal(mfa.flash_attn_func(q, k, v, causal=causal), want)
+    # MQA head expanded to every q head: head stride 0
+    km, vm = _r((B, S, 1, D), seed=4), _r((B, S, 1, D), seed=5)
+    ke, ve = km.expand(B, S, H, D), vm.expand(B, S, H, D)
+    assert ke.stride(2) == 0
+    want = mfa.flash_attn_func(q, km, vm, causal=causal)              # the same math as real MQA
+    got = mfa.flash_attn_func(q, ke, ve, causal=causal)
+    assert torch.equal(got, mfa.flash_attn_func(q, ke.contiguous(), ve.contiguous(), causal=causal))
+    assert (got.float() - want.float()).abs().max().item() <= 1e-5
+    # a broadcast q
+    q1 = _r((1, S, H, D), seed=6).expand(B, S, H, D)
+    assert torch.equal(mfa.flash_attn_func(q1, k, v, causal=causal),
+                       mfa.flash_attn_func(q1.contiguous(), k.contiguous(), v.contiguous(), causal=causal))
+
+
+def test_decode_broadcast_cache_views(mfa):
+    from oracle import ref_attention as R
+    B, KV, H, Hkv, D = 4, 700, 8, 2, 128
+    q = _r((B, 1, H, D), seed=1)
+    k1, v1 = _r((1, KV, Hkv, D), seed=2), _r((1, KV, Hkv, D), seed=3)
+    kc, vc = k1.expand(B, KV, Hkv, D), v1.expand(B, KV, Hkv, D)
+    sl = torch.tensor([700, 1, 333, 64], dtype=torch.int32, device="cuda")
+    got = mfa.flash_attn_with_kvcache(q, kc, vc, sl)
+    assert torch.equal(got, mfa.flash_attn_with_kvcache(q, kc.contiguous(), vc.contiguous(), sl))
+    assert (got.float() - R.kvcache_ref(q, kc.contiguous(), vc.contiguous(), sl)).abs().max().item() <= TOL["fp16"]
+    # broadcast q over the batch (every sequence asks the same query)
+    qb = _r((1, 1, H, D), seed=4).expand(B, 1, H, D)
+    assert torch.equal(mfa.flash_attn_with_kvcache(qb, kc, vc, sl), mfa.flash_attn_with_kvcache(qb.contiguous(), kc.contiguous(), vc.contiguous(), sl))
+
+
+def test_c_abi_rejects_zero_stride(mfa_lib):
+    """The C-ABI itself refuses a broadcast stride instead of inventing one (a non-torch caller gets an error code)."""
+    import ctypes
+    from mini_flash_attention_b200 import _lib
+    P = _lib.MfaParams()
+    S, H, D = 256, 2, 64
+    q = _r((2, S, H, D))
+    o = torch.empty_like(q)
+    P.q_ptr = P.k_ptr = P.v_ptr = q.data_ptr()
+    P.o_ptr = o.data_ptr()
+    P.q_batch_stride = P.o_batch_stride = S * H * D
+    P.k_batch_stride = P.v_batch_stride = 0          # broadcast over a batch of 2
+    P.q_row_stride = P.k_row_stride = P.v_row_stride = P.o_row_stride = H * D
+    P.q_head_stride = P.k_head_stride = P.v_head_stride = P.o_head_stride = D
+    P.heads = P.kv_heads = H
+    P.batch, P.seqlen_q, P.seqlen_k, P.head_dim = 2, S, S, D
+    rc = mfa_lib.mfa_prefill_fwd(ctypes.byref(P), None)
+    assert rc != 0
+    assert b"stride" in mfa_lib.mfa_last_error()
+
+
+@pytest.mark.parametrize("B,H", [(2, 8), (4, 10)])
+def test_persistent_grid_items_without_kv_work_bottom_right(mfa, B, H):
+    """Sq = 4096, Sk = 128, bottom-right causal: rows < Sq - Sk see no key.  16 m-blocks x B x H items > 148 CTAs, so
+    persistent CTAs walk runs of items that have no KV work at all, then an item that has (ADVICE: barrier phases)."""
+    from oracle import ref_attention as R
+    Sq, Sk, D = 4096, 128, 128
+    q, k, v = _r((B, Sq, H, D), seed=1), _r((B, Sk, H, D), seed=2), _r((B, Sk, H, D), seed=3)
+    out, lse = mfa.flash_attn_func(q, k, v, causal=True, bottom_right=True, return_lse=True)
+    assert torch.isfinite(out).all()
+    assert out[:, :Sq - Sk].abs().max().item() == 0.0
+    assert torch.isinf(lse[:, :, :Sq - Sk]).all()
+    ref = R.attention_ref(q[:, Sq - Sk:], k, v, True)     # the last Sk rows: an ordinary causal square
+    assert (out[:, Sq - Sk:].float() - ref).abs().max().item() <= TOL["fp16"]
+    # twice in a row on the same stream: the second launch starts from fresh barriers
+    assert torch.equal(out, mfa.flash_attn_func(q, k, v, causal=True, bottom_right=True))
+
+
+def test_persistent_grid_window_rows_past_the_keys(mfa):
+    """Sq > Sk + left with a top-left window: the trailing query rows see nothing; mixed with rows that do."""
+    from oracle import ref_attention as R
+    B, H, Sq, Sk, D, left = 3, 16, 2048, 512, 128, 100
+    q, k, v = _r((B, Sq, H, D), seed=4), _r((B, Sk, H, D), seed=5), _r((B, Sk, H, D), seed=6)
+    out = mfa.flash_attn_func(q, k, v, window_size=(left, 0))
+    ref = R.attention_ref(q, k, v, False, window_size=(left, 0))
+    assert (out.float() - ref).abs().max().item() <= TOL["fp16"]
+    assert out[:, Sk + left:].abs().max().item() == 0.0
+
+
+def test_persistent_grid_one_tile_items(mfa):
+    """seqlen_q <= 128 per item with many items: the second Q tile of every item has no rows at all."""
+    from oracle import ref_attention as R
+    B, H, S, D = 40, 8, 100, 128
+    q, k, v = _r((B, S, H, D), seed=7), _r((B, S, H, D), seed=8), _r((B, S, H, D), seed=9)
+    for causal in (False, True):
+        out = mfa.flash_attn_func(q, k, v, causal=causal)
+        assert (out.float() - R.attention_ref(q, k, v, causal)).abs().max().item() <= TOL["fp16"]
+
+
+def test_many_short_items_back_to_back(mfa):
+    """S = 256 ... 384 at B*H >> #SMs: every CTA crosses many item boundaries (the K/V stream runs across items)."""
+    from oracle import ref_attention as R
+    for S in (256, 257, 384):
+        q, k, v = _r((16, S, 24, 128), torch.bfloat16, S), _r((16, S, 24, 128), torch.bfloat16, S + 1), _r((16, S, 24, 128), torch.bfloat16, S + 2)
+        for causal in (False, True):
+            out = mfa.flash_attn_func(q, k, v, causal=causal)
+            assert (out.float() - R.attention_ref(q, k, v, causal)).abs().max().item() <= TOL["bf16"]
+
+
+def test_exchange_timeout_writes_nan(mfa, monkeypatch):
+    """A 2-rank exchange where rank 1 never runs: rank 0's rows must come back NaN, the status names rank 1, and
+    clear_status resets it."""
+    monkeypatch.setenv("MFA_XCHG_TIMEOUT_MS", "50")
+    from mini_flash_attention_b200 import parallel as par
+    B, Hq, Hkv, D, KV = 1, 8, 2, 128, 512
+    xs = par.KVShardExchange.local_group(2, B * Hq, D)
+    try:
+        q = _r((B, 1, Hq, D), torch.bfloat16, 1)
+        kc, vc = _r((B, KV, Hkv, D), torch.bfloat16, 2), _r((B, KV, Hkv, D), torch.bfloat16, 3)
+        sl = torch.full((B,), KV, dtype=torch.int32, device="cuda")
+        out = par.decode_kv_sharded(q, kc, vc, sl, None, world=2, exchange=xs[0])
+        torch.cuda.synchronize()
+        assert torch.isnan(out.float()).all()
+        assert xs[0].status() == 2            # 1 + the rank that did not arrive
+        assert xs[0].status(clear=True) == 2
+        assert xs[0].status() == 0
+        with pytest.raises(RuntimeError):
+            out = par.decode_kv_sharded(q, kc, vc, sl, None, world=2, exchange=xs[0])
+            xs[0].check()
+    finally:
+        for x in xs:
+            x.close()
