@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define MFA_B200_ABI_VERSION 3
+#define MFA_B200_ABI_VERSION 4
 
 /* error codes (0 == success).  mfa_last_error() returns the message of the last failure on the
  * calling thread. */
@@ -102,6 +102,16 @@ typedef struct mfa_params {
      * window_size convention).  KV tiles outside the band are skipped.  0 = the reference's behaviour: the two window
      * fields are ignored (flash.h:33-34, README.md:153 "not implemented").  New. */
     int32_t local_window;
+    /* e4m3 KV cache, DECODE only (the reference gates the dtype to fp16/bf16, api.cpp:126-129): half the
+     * HBM bytes per key.  kv_fp8 != 0: k_ptr / v_ptr point at 1-byte e4m3 elements (the K/V strides stay in ELEMENTS, i.e.
+     * bytes, and must be multiples of 16); the dequantised element is byte_value * scale with
+     * scale = k_scale_ptr[kv_head * kv_scale_stride] (NULL => 1).  q / out keep the 16-bit type of is_bf16; the tiles are
+     * converted to fp16 in registers (exact) and the MMAs run in fp16 (a bf16 q beyond the fp16 range saturates).
+     * head_dim must be a multiple of 128.  mfa_prefill_fwd and mfa_kvcache_append reject kv_fp8.  New in ABI v4. */
+    int32_t kv_fp8;
+    int32_t kv_scale_stride;             /* 1: one scale per KV head; 0: one scale for the whole tensor */
+    const float* k_scale_ptr;            /* device, fp32 */
+    const float* v_scale_ptr;
 } mfa_params_t;
 
 /* --- introspection ------------------------------------------------------------------------ */

@@ -46,6 +46,8 @@ def _tma_ok(t: torch.Tensor) -> bool:
     """TMA needs a 16-byte aligned base and 16-byte multiples for every non-innermost stride."""
     if t.data_ptr() % 16:
         return False
+    if t.element_size() == 1:   # e4m3 cache: 16 elements per 16 bytes
+        return all(s % 16 == 0 and (s > 0 or n <= 1) for s, n in zip(t.stride()[:-1], t.shape[:-1])) and t.stride(-1) == 1
     # a broadcast view (expand(): stride 0 on an extent > 1) cannot be expressed by a tensor map either
     return all(s % 8 == 0 and (s > 0 or n <= 1) for s, n in zip(t.stride()[:-1], t.shape[:-1])) and t.stride(-1) == 1
 
@@ -194,9 +196,34 @@ def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max
     return (out, lse) if _want_lse else out
 
 
-def _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits):
+_FP8 = getattr(torch, "float8_e4m3fn", None)
+
+
+def _kv_scale(s, kv_heads: int, device):
+    """k_scale / v_scale of an e4m3 cache -> (kv_heads,) fp32 device tensor (None stays None = 1.0)."""
+    if s is None:
+        return None
+    if not isinstance(s, torch.Tensor):
+        s = torch.full((1,), float(s), dtype=torch.float32, device=device)
+    _check(s.is_cuda, "k_scale / v_scale must be on CUDA (or Python floats)")
+    _check(s.numel() in (1, kv_heads), "k_scale / v_scale must have 1 or kv_num_heads elements")
+    return s.to(torch.float32).reshape(-1).expand(kv_heads).contiguous()
+
+
+def _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, k_scale=None, v_scale=None):
     """Validation + parameter block shared by the decode entry points.  api.cpp:343-433."""
-    _check_qkv(q, k_cache, v_cache)
+    fp8 = _FP8 is not None and k_cache.dtype == _FP8
+    if fp8:
+        # e4m3 cache (SURVEY 8f row 4; the reference gates the dtype at api.cpp:126-129): q keeps its 16-bit type
+        _check(q.dtype in (torch.float16, torch.bfloat16), "FlashAttention only support fp16 and bf16 data type")
+        _check(v_cache.dtype == _FP8, "k_cache and v_cache must have the same dtype")
+        _check(q.is_cuda and k_cache.is_cuda and v_cache.is_cuda, "q, k_cache and v_cache must be on CUDA")
+        _check(q.stride(-1) == 1 and k_cache.stride(-1) == 1 and v_cache.stride(-1) == 1,
+               "Input tensor must have contiguous last dimension")
+        _check(q.shape[-1] % 128 == 0, "an e4m3 KV cache needs head_dim to be a multiple of 128")
+    else:
+        _check(k_scale is None and v_scale is None, "k_scale / v_scale are for an e4m3 (torch.float8_e4m3fn) cache")
+        _check_qkv(q, k_cache, v_cache)
     _check(q.dim() == 4, "q must have shape (batch, 1, num_heads, head_dim)")
     batch, seqlen_q, num_heads, head_dim = q.shape
     _check(seqlen_q == 1, f"flash decoding expects seqlen_q == 1, got {seqlen_q}")  # api.cpp:377
@@ -248,18 +275,25 @@ def _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits):
     P.seqlen_q, P.seqlen_k, P.head_dim = 1, seqlen_k, head_dim
     P.is_bf16 = int(q.dtype == torch.bfloat16)
     P.num_splits = int(num_splits)
+    if fp8:
+        ks, vs = _kv_scale(k_scale, kv_num_heads, q.device), _kv_scale(v_scale, kv_num_heads, q.device)
+        keep += [ks, vs]
+        P.kv_fp8, P.kv_scale_stride = 1, 1
+        P.k_scale_ptr = ks.data_ptr() if ks is not None else None
+        P.v_scale_ptr = vs.data_ptr() if vs is not None else None
     return P, keep
 
 
 def mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens: Optional[Union[int, torch.Tensor]],
                                       block_table, causal, num_splits=0, _want_lse=False, _k_new=None, _v_new=None,
-                                      _window_left=-1):
+                                      _window_left=-1, _k_scale=None, _v_scale=None):
     """q_len == 1 decode over a contiguous or paged KV cache.  api.cpp:343-446.
     `causal` is accepted and ignored exactly like the reference (api.cpp:349, quirk Q10)."""
-    P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
+    P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, _k_scale, _v_scale)
     if _window_left is not None and _window_left >= 0:  # sliding window (SURVEY 8f row 3): the last window_left + 1 keys
         P.local_window, P.window_size_left, P.window_size_right = 1, int(_window_left), -1
     if _k_new is not None or _v_new is not None:
+        _check(not P.kv_fp8, "appending k/v into an e4m3 cache is not supported (quantise and write the rows yourself)")
         keep.append(_append_kv(P, keep, q, k_cache, v_cache, cache_seqlens, _k_new, _v_new))
     out = torch.empty_like(q)  # api.cpp:405
     # (B, H, 1) fp32: the tensor the reference allocates and drops (api.cpp:436-437)
@@ -438,6 +472,15 @@ def mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, bl
     return r if return_lse else (r, None)
 
 
+def mini_flash_attention_with_kvcache_fp8(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, return_lse,
+                                          window_left, k_scale, v_scale):
+    """Decode over an e4m3 (torch.float8_e4m3fn) KV cache with per-tensor or per-KV-head dequantisation scales."""
+    r = _py_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, False, num_splits, _want_lse=return_lse,
+                         _window_left=window_left, _k_scale=k_scale, _v_scale=v_scale)
+    return r if return_lse else (r, None)
+
+
+_py_with_kvcache_fp8 = mini_flash_attention_with_kvcache_fp8
 _py_forward_ext = mini_flash_attention_forward_ext
 _py_varlen_forward_ext = mini_flash_attention_varlen_forward_ext
 _py_with_kvcache_ext = mini_flash_attention_with_kvcache_ext
@@ -459,7 +502,7 @@ def _load_compiled_shim():
         if _os.environ.get("MFA_B200_SHIM", "").lower() in ("cpp", "compiled"):
             raise
         return None
-    if not hasattr(m, "mini_flash_attention_with_kvcache_ext"):   # built from an older torch_shim.cpp: rebuild with build()
+    if not hasattr(m, "mini_flash_attention_with_kvcache_fp8"):   # built from an older torch_shim.cpp: rebuild with build()
         _shim_error = ImportError("stale _mfa_torch_shim module (run python -m mini_flash_attention_b200.build)")
         return None
     return m
@@ -498,6 +541,15 @@ if _shim is not None:
             cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
         return _shim.mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal,
                                                            num_splits, return_lse, k_new, v_new, window_left)
+
+    def mini_flash_attention_with_kvcache_fp8(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, return_lse,  # noqa: F811
+                                              window_left, k_scale, v_scale):
+        if isinstance(cache_seqlens, int):
+            cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
+        kv_heads = k_cache.shape[-2]
+        return _shim.mini_flash_attention_with_kvcache_fp8(q, k_cache, v_cache, cache_seqlens, block_table, num_splits,
+                                                           return_lse, window_left, _kv_scale(k_scale, kv_heads, q.device),
+                                                           _kv_scale(v_scale, kv_heads, q.device))
 
     _py_decode_kv_sharded_fused = decode_kv_sharded_fused
 

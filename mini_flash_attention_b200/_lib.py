@@ -13,7 +13,7 @@ _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MFA_B200_LIB") or os.path.join(_PKG_DIR, "libmfa_b200.so")
 
 MFA_OK = 0
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class MfaParams(ctypes.Structure):
@@ -41,6 +41,8 @@ class MfaParams(ctypes.Structure):
         ("softmax_lse_ptr", ctypes.c_void_p),
         ("partial_out", ctypes.c_int32), ("causal_bottom_right", ctypes.c_int32),
         ("local_window", ctypes.c_int32),
+        ("kv_fp8", ctypes.c_int32), ("kv_scale_stride", ctypes.c_int32),
+        ("k_scale_ptr", ctypes.c_void_p), ("v_scale_ptr", ctypes.c_void_p),
     ]
 
 

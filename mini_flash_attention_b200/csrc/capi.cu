@@ -140,6 +140,7 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     int rc = check_common(p);
     if (rc) return rc;
     if ((rc = check_device())) return rc;
+    if (p->kv_fp8) return fail(MFA_ERR_UNSUPPORTED, "an e4m3 K/V is supported by the decode entry points only");
     const bool varlen = p->cu_seqlens_q != nullptr;
     const bool paged = p->block_table != nullptr;
     if (varlen && !p->cu_seqlens_k) return fail(MFA_ERR_INVALID_ARG, "cu_seqlens_k must be given with cu_seqlens_q");
@@ -326,8 +327,15 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
     if (p->seqlen_q != 1) return fail(MFA_ERR_INVALID_ARG, "flash decoding expects seqlen_q == 1, got %d", p->seqlen_q);
     if (p->seqlen_k <= 0) return fail(MFA_ERR_INVALID_ARG, "KV cache has no rows");
     const bool paged = p->block_table != nullptr;
+    const bool fp8 = p->kv_fp8 != 0;
+    const int64_t smul = fp8 ? 16 : 8;   // elements per 16 bytes
+    auto mult8 = [smul](int64_t x) { return (x % smul) == 0; };   // (shadows the 16-bit helper: every cache stride check below)
+    if (fp8 && (p->head_dim % 128))
+        return fail(MFA_ERR_UNSUPPORTED, "an e4m3 KV cache needs head_dim to be a multiple of 128 (got %d)", p->head_dim);
+    if (fp8 && p->kv_scale_stride != 0 && p->kv_scale_stride != 1)
+        return fail(MFA_ERR_INVALID_ARG, "kv_scale_stride must be 0 (per tensor) or 1 (per KV head)");
     if (!mult8(p->k_row_stride) || !mult8(p->k_head_stride) || !mult8(p->v_row_stride) || !mult8(p->v_head_stride))
-        return fail(MFA_ERR_UNSUPPORTED, "cache row/head strides must be multiples of 8 elements (16 bytes)");
+        return fail(MFA_ERR_UNSUPPORTED, "cache row/head strides must be multiples of 16 bytes");
     if ((p->q_head_stride % 2) || (p->q_batch_stride % 2) || (reinterpret_cast<uintptr_t>(p->q_ptr) & 3))
         return fail(MFA_ERR_UNSUPPORTED, "q strides must be even and q 4-byte aligned");
     if (p->partial_out) {
@@ -371,18 +379,28 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
         const uint64_t dims[4] = {(uint64_t)D, (uint64_t)page, (uint64_t)p->kv_heads, (uint64_t)p->num_blocks};
         const int64_t ks[4] = {1, p->k_row_stride, p->k_head_stride, p->k_cache_block_stride};
         const int64_t vs[4] = {1, p->v_row_stride, p->v_head_stride, p->v_cache_block_stride};
-        const uint32_t box[4] = {64, (uint32_t)box_rows, 1, 1};
-        if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k_cache: %s", err);
-        if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v_cache: %s", err);
+        const uint32_t box[4] = {fp8 ? 128u : 64u, (uint32_t)box_rows, 1, 1};   // 128 bytes per box row either way
+        if (fp8) {
+            if ((err = mfa::encode_tmap_4d_u8(&tmK, p->k_ptr, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k_cache: %s", err);
+            if ((err = mfa::encode_tmap_4d_u8(&tmV, p->v_ptr, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v_cache: %s", err);
+        } else {
+            if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k_cache: %s", err);
+            if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v_cache: %s", err);
+        }
     } else {
         if (!mult8(p->k_batch_stride) || !mult8(p->v_batch_stride))
             return fail(MFA_ERR_UNSUPPORTED, "cache batch strides must be multiples of 8 elements");
         const uint64_t dims[4] = {(uint64_t)D, (uint64_t)p->seqlen_k, (uint64_t)p->kv_heads, (uint64_t)p->batch};
         const int64_t ks[4] = {1, p->k_row_stride, p->k_head_stride, p->k_batch_stride};
         const int64_t vs[4] = {1, p->v_row_stride, p->v_head_stride, p->v_batch_stride};
-        const uint32_t box[4] = {64, (uint32_t)box_rows, 1, 1};
-        if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k_cache: %s", err);
-        if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v_cache: %s", err);
+        const uint32_t box[4] = {fp8 ? 128u : 64u, (uint32_t)box_rows, 1, 1};   // 128 bytes per box row either way
+        if (fp8) {
+            if ((err = mfa::encode_tmap_4d_u8(&tmK, p->k_ptr, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k_cache: %s", err);
+            if ((err = mfa::encode_tmap_4d_u8(&tmV, p->v_ptr, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v_cache: %s", err);
+        } else {
+            if ((err = mfa::encode_tmap_4d(&tmK, p->k_ptr, bf16, dims, ks, box))) return fail(MFA_ERR_UNSUPPORTED, "k_cache: %s", err);
+            if ((err = mfa::encode_tmap_4d(&tmV, p->v_ptr, bf16, dims, vs, box))) return fail(MFA_ERR_UNSUPPORTED, "v_cache: %s", err);
+        }
     }
 
     const size_t rows = (size_t)p->batch * (size_t)p->heads;
@@ -418,6 +436,10 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
     kp.window_left = (p->local_window && p->window_size_left >= 0) ? p->window_size_left : -1;
     kp.scale = p->softmax_scale > 0.f ? p->softmax_scale : 1.0f / std::sqrt((float)D);
     kp.scale_log2 = kp.scale * 1.4426950408889634f;
+    kp.kv_fp8 = fp8 ? 1 : 0;
+    kp.kv_scale_stride = p->kv_scale_stride;
+    kp.k_scale = fp8 ? p->k_scale_ptr : nullptr;
+    kp.v_scale = fp8 ? p->v_scale_ptr : nullptr;
 
     cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
     cudaError_t e = mfa::launch_decode(tmK, tmV, kp, bf16, dpad, stream);

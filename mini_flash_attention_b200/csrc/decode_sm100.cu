@@ -18,6 +18,8 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
+#include <type_traits>
+
 #include "kparams.h"
 #include "merge.cuh"
 #include "ptx.cuh"
@@ -73,6 +75,18 @@ __device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
                  : "r"(addr));
 }
 
+// two e4m3 bytes (low 16 bits of x) -> packed f16x2 (exact: e4m3 is a subset of fp16)
+__device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t x) {
+    uint32_t r;
+    asm("{\n\t.reg .b16 t;\n\tcvt.u16.u32 t, %1;\n\tcvt.rn.f16x2.e4m3x2 %0, t;\n\t}" : "=r"(r) : "r"(x));
+    return r;
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+}
+
 // Byte offset of 16-byte chunk `chunk` (0 .. DPAD/8) of row `row` inside a [DPAD/64][64 rows][128 B] tile
 // written by TMA with CU_TENSOR_MAP_SWIZZLE_128B (tile base 1024-byte aligned).
 template <int ROWS>
@@ -87,14 +101,19 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk) {
 // __launch_bounds__(160, 3) (128 registers, -DMFA_DECODE_MINBLOCKS=3) is 13 % slower (6313 GB/s at KV=8192).
 #define MFA_DECODE_STAGES 2
 #endif
-template <int DPAD>
+template <int DPAD, bool KV8 = false>
 struct DecodeCfg {
     static constexpr int kTile = kDecodeTileRows;
-    static constexpr int kTileBytes = kTile * DPAD * 2;          // one of K or V
+    static constexpr int kEB = KV8 ? 1 : 2;                      // bytes per cache element (e4m3 cache: 1)
+    static constexpr int kSub = DPAD * kEB / 128;                // 128-byte wide sub-tiles per row
+    static constexpr int kBoxElems = 128 / kEB;                  // elements per 128-byte box row
+    static constexpr int kTileBytes = kTile * DPAD * kEB;        // one of K or V
     static constexpr int kStageBytes = 2 * kTileBytes;           // K then V
-    static constexpr int kStages = (DPAD == 64) ? 2 * MFA_DECODE_STAGES : MFA_DECODE_STAGES;
+    static constexpr int kStages = (DPAD * kEB == 128) ? 2 * MFA_DECODE_STAGES : MFA_DECODE_STAGES;   // >= 32 KB per stage pair
     static constexpr int kRingBytes = kStages * kStageBytes;
-    static constexpr int kSmemBytes = kRingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int kMergeBytes = 4 * 16 * DPAD * 4 + 512;  // cross-warp merge staging (aliases the ring)
+    static constexpr int kBarOffset = kRingBytes > kMergeBytes ? kRingBytes : kMergeBytes;
+    static constexpr int kSmemBytes = kBarOffset + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 // (tuning aid: -DMFA_DECODE_MINBLOCKS=3 adds a min-blocks launch bound at head_dim <= 128.  Even a bound of 1 changes
@@ -105,19 +124,27 @@ struct DecodeCfg {
 #else
 #define MFA_DECODE_BOUNDS(DP) __launch_bounds__(kDecodeThreads)
 #endif
-template <typename T, int DPAD>
+// KV8: the cache holds e4m3 bytes -- half the HBM bytes per key.  The tiles are converted to fp16 in
+// registers (cvt.rn.f16x2.e4m3x2, exact) right before the MMAs, which then always run in fp16 (q is converted once per
+// CTA; a bf16 q beyond the fp16 range saturates); the per-KV-head dequantisation scales are folded into the softmax
+// scale (K) and into the final normalisation (V).  The MMA k / n indices are PERMUTED relative to head_dim so that one
+// ldmatrix of the 1-byte tile feeds whole fragments: a thread's four bytes of a K row are d = 16c + 4tq + {0,1,2,3}
+// (k-step c), and the transposed V load yields the kv-row pairs of an even and an odd head_dim column.
+template <typename T, int DPAD, bool KV8>
 __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_constant__ CUtensorMap tmK,
                                                                         const __grid_constant__ CUtensorMap tmV,
                                                                         const __grid_constant__ DecodeKParams p) {
-    using Cfg = DecodeCfg<DPAD>;
+    using Cfg = DecodeCfg<DPAD, KV8>;
+    using TM = typename std::conditional<KV8, __half, T>::type;   // MMA operand type
     constexpr int kTile = Cfg::kTile;
     constexpr int kStages = Cfg::kStages;
     constexpr int KS = DPAD / 16;   // k-steps of QK^T
     constexpr int NT = DPAD / 8;    // n-tiles of PV
+    constexpr int kSub = Cfg::kSub;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kRingBytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kBarOffset);
     uint64_t* empty_bar = full_bar + kStages;
 
     const int split = blockIdx.x;
@@ -164,7 +191,7 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
                 const int row0 = (t0 + it) * kTile;
                 const int rows_valid = min(len - row0, kTile);
                 const int nchunks = (rows_valid + p.box_rows - 1) / p.box_rows;
-                mbar_arrive_expect_tx(&full_bar[s], static_cast<uint32_t>(nchunks * chunk_bytes * (DPAD / 64) * 2));
+                mbar_arrive_expect_tx(&full_bar[s], static_cast<uint32_t>(nchunks * chunk_bytes * kSub * 2));
                 uint8_t* kdst = smem + s * Cfg::kStageBytes;
                 uint8_t* vdst = kdst + Cfg::kTileBytes;
                 for (int c = 0; c < nchunks; ++c) {
@@ -179,11 +206,11 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
                         blk = b;
                     }
 #pragma unroll
-                    for (int hf = 0; hf < DPAD / 64; ++hf) {
-                        tma_load_4d(kdst + hf * (kTile * 128) + c * chunk_bytes, &tmK, &full_bar[s], hf * 64, in_page, kh,
-                                    blk);
-                        tma_load_4d(vdst + hf * (kTile * 128) + c * chunk_bytes, &tmV, &full_bar[s], hf * 64, in_page, kh,
-                                    blk);
+                    for (int hf = 0; hf < kSub; ++hf) {
+                        tma_load_4d(kdst + hf * (kTile * 128) + c * chunk_bytes, &tmK, &full_bar[s], hf * Cfg::kBoxElems,
+                                    in_page, kh, blk);
+                        tma_load_4d(vdst + hf * (kTile * 128) + c * chunk_bytes, &tmV, &full_bar[s], hf * Cfg::kBoxElems,
+                                    in_page, kh, blk);
                     }
                 }
             }
@@ -200,20 +227,34 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
     uint32_t qa[KS][4];
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
-        const int c = ks * 16 + tq * 2;
         const T* q0 = qbase + (int64_t)(head0 + g0) * p.q_head_stride;
         const T* q1 = qbase + (int64_t)(head0 + g1) * p.q_head_stride;
+        // 16-bit cache: MMA k index = head_dim index.  e4m3 cache: k-step ks covers d = 16 ks .. 16 ks + 15 with the
+        // thread's k pairs (2tq, 2tq+1) / (2tq+8, 2tq+9) mapped to d = 16 ks + 4tq + {0,1} / {2,3} (see the K fragments)
+        const int c = KV8 ? (ks * 16 + tq * 4) : (ks * 16 + tq * 2);
+        const int c_hi = KV8 ? (c + 2) : (c + 8);
         qa[ks][0] = (g0 < gvalid && c < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q0 + c) : 0u;
         qa[ks][1] = (g1 < gvalid && c < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q1 + c) : 0u;
-        qa[ks][2] = (g0 < gvalid && c + 8 < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q0 + c + 8) : 0u;
-        qa[ks][3] = (g1 < gvalid && c + 8 < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q1 + c + 8) : 0u;
+        qa[ks][2] = (g0 < gvalid && c_hi < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q0 + c_hi) : 0u;
+        qa[ks][3] = (g1 < gvalid && c_hi < p.head_dim) ? *reinterpret_cast<const uint32_t*>(q1 + c_hi) : 0u;
+        if constexpr (KV8 && !std::is_same<T, __half>::value) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {   // bf16 pair -> fp16 pair (the MMAs of the e4m3 path run in fp16)
+                const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&qa[ks][e]);
+                const __half2 h = __floats2half2_rn(__low2float(b), __high2float(b));
+                qa[ks][e] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+        }
     }
 
     float o[NT][4];
 #pragma unroll
     for (int i = 0; i < NT; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
     float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-    const float c2 = p.scale_log2;
+    // e4m3 cache: S = (q . k_bytes) * k_scale * softmax_scale -- fold the per-KV-head K scale into the exp2 scale
+    const float k_descale = (KV8 && p.k_scale) ? p.k_scale[kh * p.kv_scale_stride] : 1.f;
+    const float v_descale = (KV8 && p.v_scale) ? p.v_scale[kh * p.kv_scale_stride] : 1.f;
+    const float c2 = p.scale_log2 * k_descale;
     const int wrow = warp * 16;   // this warp's rows inside each tile
 
     for (int it = 0; it < ntiles; ++it) {
@@ -232,7 +273,7 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
             for (int r = max(rows_valid - wrow, 0); r < 16; ++r) {
                 const int row = wrow + r;
 #pragma unroll
-                for (int hf = 0; hf < DPAD / 64; ++hf)
+                for (int hf = 0; hf < kSub; ++hf)
                     *reinterpret_cast<uint32_t*>(vt + hf * (kTile * 128) + row * 128 + lane * 4) = 0u;
             }
             fence_proxy_async_smem();   // generic writes ordered before the next TMA refill of this stage
@@ -246,12 +287,26 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
         {
             const int mi = lane >> 3, r = lane & 7;
             const int row = wrow + (mi >> 1) * 8 + r;
+            if constexpr (KV8) {
+                // one ldmatrix.x4 = 16 kv rows x 32 bytes = two k-steps of both n-tiles; a thread's register of matrix
+                // (n-tile, chunk) holds the row's bytes d = 16 chunk + 4tq + {0,1,2,3}: low pair -> b0, high pair -> b1
 #pragma unroll
-            for (int ks = 0; ks < KS; ++ks) {
-                uint32_t kb[4];
-                ldsm_x4(kb, kaddr + swz_off<kTile>(row, 2 * ks + (mi & 1)));
-                mma_16816<T>(sc[0], qa[ks], kb[0], kb[1]);
-                mma_16816<T>(sc[1], qa[ks], kb[2], kb[3]);
+                for (int k2 = 0; k2 < KS / 2; ++k2) {
+                    uint32_t kb[4];
+                    ldsm_x4(kb, kaddr + swz_off<kTile>(row, 2 * k2 + (mi & 1)));
+                    mma_16816<TM>(sc[0], qa[2 * k2], e4m3x2_to_f16x2(kb[0]), e4m3x2_to_f16x2(kb[0] >> 16));
+                    mma_16816<TM>(sc[0], qa[2 * k2 + 1], e4m3x2_to_f16x2(kb[1]), e4m3x2_to_f16x2(kb[1] >> 16));
+                    mma_16816<TM>(sc[1], qa[2 * k2], e4m3x2_to_f16x2(kb[2]), e4m3x2_to_f16x2(kb[2] >> 16));
+                    mma_16816<TM>(sc[1], qa[2 * k2 + 1], e4m3x2_to_f16x2(kb[3]), e4m3x2_to_f16x2(kb[3] >> 16));
+                }
+            } else {
+#pragma unroll
+                for (int ks = 0; ks < KS; ++ks) {
+                    uint32_t kb[4];
+                    ldsm_x4(kb, kaddr + swz_off<kTile>(row, 2 * ks + (mi & 1)));
+                    mma_16816<TM>(sc[0], qa[ks], kb[0], kb[1]);
+                    mma_16816<TM>(sc[1], qa[ks], kb[2], kb[3]);
+                }
             }
         }
         // ---- tail mask (decode.cuh:327-336)
@@ -308,19 +363,37 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
         }
         // ---- O += P V
         uint32_t pa[4];
-        pa[0] = Pack2<T>::pack(sc[0][0], sc[0][1]);
-        pa[1] = Pack2<T>::pack(sc[0][2], sc[0][3]);
-        pa[2] = Pack2<T>::pack(sc[1][0], sc[1][1]);
-        pa[3] = Pack2<T>::pack(sc[1][2], sc[1][3]);
+        pa[0] = Pack2<TM>::pack(sc[0][0], sc[0][1]);
+        pa[1] = Pack2<TM>::pack(sc[0][2], sc[0][3]);
+        pa[2] = Pack2<TM>::pack(sc[1][0], sc[1][1]);
+        pa[3] = Pack2<TM>::pack(sc[1][2], sc[1][3]);
         {
             const int mi = lane >> 3, r = lane & 7;
             const int row = wrow + (mi & 1) * 8 + r;
+            if constexpr (KV8) {
+                // transposed load of the byte tile in 16-bit units: a thread's register of matrix (kv half, chunk) holds
+                // {V[2tq][d], V[2tq][d+1], V[2tq+1][d], V[2tq+1][d+1]}, d = 16 chunk + 2 (lane / 4): bytes (0,2) are the
+                // kv-row pair of the EVEN column, bytes (1,3) of the ODD one.  N-tile 4 n4 + 2 cc + e (chunk 2 n4 + cc,
+                // parity e) therefore has MMA column n <-> d = 16 chunk + 2 n + e; the epilogue undoes the permutation.
 #pragma unroll
-            for (int n2 = 0; n2 < NT / 2; ++n2) {
-                uint32_t vb[4];
-                ldsm_x4_trans(vb, vaddr + swz_off<kTile>(row, 2 * n2 + (mi >> 1)));
-                mma_16816<T>(o[2 * n2], pa, vb[0], vb[1]);
-                mma_16816<T>(o[2 * n2 + 1], pa, vb[2], vb[3]);
+                for (int n4 = 0; n4 < NT / 4; ++n4) {
+                    uint32_t vb[4];
+                    ldsm_x4_trans(vb, vaddr + swz_off<kTile>(row, 2 * n4 + (mi >> 1)));
+#pragma unroll
+                    for (int cc = 0; cc < 2; ++cc) {
+                        const uint32_t lo = vb[2 * cc], hi = vb[2 * cc + 1];   // kv rows 0-7 / 8-15 of the warp's 16
+                        mma_16816<TM>(o[4 * n4 + 2 * cc], pa, e4m3x2_to_f16x2(prmt(lo, 0u, 0x4420u)), e4m3x2_to_f16x2(prmt(hi, 0u, 0x4420u)));
+                        mma_16816<TM>(o[4 * n4 + 2 * cc + 1], pa, e4m3x2_to_f16x2(prmt(lo, 0u, 0x4431u)), e4m3x2_to_f16x2(prmt(hi, 0u, 0x4431u)));
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int n2 = 0; n2 < NT / 2; ++n2) {
+                    uint32_t vb[4];
+                    ldsm_x4_trans(vb, vaddr + swz_off<kTile>(row, 2 * n2 + (mi >> 1)));
+                    mma_16816<TM>(o[2 * n2], pa, vb[0], vb[1]);
+                    mma_16816<TM>(o[2 * n2 + 1], pa, vb[2], vb[3]);
+                }
             }
         }
         __syncwarp();
@@ -343,13 +416,25 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
         stage_l[warp * 16 + g0] = l0;
         stage_l[warp * 16 + g1] = l1;
     }
+    if constexpr (KV8) {
+        // undo the n permutation of the e4m3 P.V: n-tiles (2c, 2c+1) hold the even / odd columns of d = 16c .. 16c+15
 #pragma unroll
-    for (int i = 0; i < NT; ++i) {
-        const int col = i * 8 + tq * 2;
-        float* w0 = stage_o + (warp * 16 + g0) * DPAD + col;
-        float* w1 = stage_o + (warp * 16 + g1) * DPAD + col;
-        *reinterpret_cast<float2*>(w0) = make_float2(o[i][0], o[i][1]);
-        *reinterpret_cast<float2*>(w1) = make_float2(o[i][2], o[i][3]);
+        for (int c = 0; c < NT / 2; ++c) {
+            const int col = c * 16 + tq * 4;
+            float* w0 = stage_o + (warp * 16 + g0) * DPAD + col;
+            float* w1 = stage_o + (warp * 16 + g1) * DPAD + col;
+            *reinterpret_cast<float4*>(w0) = make_float4(o[2 * c][0], o[2 * c + 1][0], o[2 * c][1], o[2 * c + 1][1]);
+            *reinterpret_cast<float4*>(w1) = make_float4(o[2 * c][2], o[2 * c + 1][2], o[2 * c][3], o[2 * c + 1][3]);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < NT; ++i) {
+            const int col = i * 8 + tq * 2;
+            float* w0 = stage_o + (warp * 16 + g0) * DPAD + col;
+            float* w1 = stage_o + (warp * 16 + g1) * DPAD + col;
+            *reinterpret_cast<float2*>(w0) = make_float2(o[i][0], o[i][1]);
+            *reinterpret_cast<float2*>(w1) = make_float2(o[i][2], o[i][3]);
+        }
     }
     named_bar_sync(1, 128);
 
@@ -369,7 +454,7 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
             wgt[w] = (mw[w] == -INFINITY) ? 0.f : exp2f((mw[w] - mx) * c2);
             L += stage_l[w * 16 + hr] * wgt[w];
         }
-        const float inv = (L > 0.f) ? 1.f / L : 0.f;
+        const float inv = (L > 0.f) ? v_descale / L : 0.f;   // (e4m3 cache: the V scale rides on the normalisation)
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int w = 0; w < 4; ++w) {
@@ -384,7 +469,7 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
         acc.z *= inv;
         acc.w *= inv;
         const int head = head0 + hr;
-        const float lse = (L > 0.f) ? mx * p.scale + __logf(L) : -INFINITY;   // decode.cuh:649
+        const float lse = (L > 0.f) ? mx * (p.scale * k_descale) + __logf(L) : -INFINITY;   // decode.cuh:649
         if (col < p.head_dim) {
             if (write_partial) {
                 float* dst = p.o_part + (((int64_t)split * p.batch + b) * p.heads + head) * p.head_dim + col;
@@ -448,11 +533,11 @@ __global__ void __launch_bounds__(kMergeThreads) combine_kernel(const __grid_con
 }  // namespace
 
 // ---------------------------------------------------------------------------------- launchers
-template <typename T, int DPAD>
+template <typename T, int DPAD, bool KV8 = false>
 static cudaError_t launch_decode_t(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeKParams& p,
                                    cudaStream_t stream) {
-    using Cfg = DecodeCfg<DPAD>;
-    auto kern = decode_splitkv_kernel<T, DPAD>;
+    using Cfg = DecodeCfg<DPAD, KV8>;
+    auto kern = decode_splitkv_kernel<T, DPAD, KV8>;
     static bool attr_done[64] = {};   // per (T, DPAD) instantiation and device
     int dev = 0;
     cudaGetDevice(&dev);
@@ -472,6 +557,15 @@ cudaError_t launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const 
     case DP:                                                                                 \
         return is_bf16 ? launch_decode_t<__nv_bfloat16, DP>(tmK, tmV, p, stream)             \
                        : launch_decode_t<__half, DP>(tmK, tmV, p, stream);
+    if (p.kv_fp8) {   // e4m3 cache: head_dim 128 / 256 (whole 128-byte rows)
+        if (dpad == 128)
+            return is_bf16 ? launch_decode_t<__nv_bfloat16, 128, true>(tmK, tmV, p, stream)
+                           : launch_decode_t<__half, 128, true>(tmK, tmV, p, stream);
+        if (dpad == 256)
+            return is_bf16 ? launch_decode_t<__nv_bfloat16, 256, true>(tmK, tmV, p, stream)
+                           : launch_decode_t<__half, 256, true>(tmK, tmV, p, stream);
+        return cudaErrorInvalidValue;
+    }
     switch (dpad) {
         MFA_DECODE_CASE(64)
         MFA_DECODE_CASE(128)

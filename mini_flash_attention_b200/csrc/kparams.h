@@ -31,6 +31,11 @@ struct DecodeKParams {
     int32_t partial_out;
     int32_t window_left;       // >= 0: sliding window, the query (position len - 1) sees keys >= len - 1 - window_left; < 0: all
     float scale, scale_log2;
+    // e4m3 KV cache: 1-byte elements, dequantised value = byte value * scale[kv_head * kv_scale_stride]
+    int32_t kv_fp8;
+    int32_t kv_scale_stride;   // 1 = one scale per KV head, 0 = one scale for the tensor
+    const float* k_scale;      // device; null => 1
+    const float* v_scale;
 };
 
 struct CombineKParams {

@@ -51,6 +51,12 @@
 #ifndef MFA_PSPLIT
 #define MFA_PSPLIT 1
 #endif
+// MFA_EARLY_S 1 (flat stream): a Q tile that finishes an item one KV step before the other (the causal mask: tile 0 has
+// one KV tile less than tile 1) gets the NEXT item's first S in that step already, so its softmax warpgroup works
+// through the other tile's lone last step instead of idling.
+#ifndef MFA_EARLY_S
+#define MFA_EARLY_S 1
+#endif
 #ifndef MFA_PARRIVE_WARP
 #define MFA_PARRIVE_WARP 0
 #endif
@@ -297,7 +303,11 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    // The CTA allocates ALL 512 TMEM columns (one CTA per SM), so the allocation can only start at column 0, lane 0:
+    // every TMEM address below is a compile-time constant (no register, no address arithmetic in the 72-register MMA
+    // warp).  Checked, not assumed.
+    if (*tmem_slot != 0u) __trap();
+    constexpr uint32_t tmem_base = 0u;
 
     // Register re-balancing: the launch gives every thread 168 registers (65536 / 384 threads); the
     // data-movement warpgroup hands most of its share to the two softmax warpgroups (whole S row in registers).
@@ -520,7 +530,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 if (elect_one()) {
                     const uint32_t qa = opaque(q_addr) + i * Cfg::kQTileBytes;
                     const uint32_t ka = opaque(ring_addr) + stage * Cfg::kKVTileBytes;
-                    const uint32_t tb = opaque(tmem_base);
+                    constexpr uint32_t tb = tmem_base;
 #pragma unroll
                     for (int ks = 0; ks < DPAD / 16; ++ks)
                         umma_ss(tb + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
@@ -532,7 +542,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             auto issue_PV = [&](int i, int stage, bool accumulate, int ks0, int ks1, bool commit_o) {
                 if (elect_one()) {
                     const uint32_t va = opaque(ring_addr) + stage * Cfg::kKVTileBytes;
-                    const uint32_t tb = opaque(tmem_base);
+                    constexpr uint32_t tb = tmem_base;
 #pragma unroll
                     for (int ks = ks0; ks < ks1; ++ks)
                         umma_ts(tb + Cfg::kTmemO + i * DPAD, tb + Cfg::kTmemS + i * 128 + ks * 8,
@@ -543,7 +553,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             };
             auto issue_PV_at = [&](int i, uint32_t va, bool accumulate, int ks0, int ks1, bool commit_o) {
                 if (elect_one()) {
-                    const uint32_t tb = opaque(tmem_base);
+                    constexpr uint32_t tb = tmem_base;
 #pragma unroll
                     for (int ks = ks0; ks < ks1; ++ks)
                         umma_ts(tb + Cfg::kTmemO + i * DPAD, tb + Cfg::kTmemS + i * 128 + ks * 8,
@@ -588,7 +598,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                         }
                         if (elect_one()) {
                             const uint32_t qa = opaque(q_addr) + i * Cfg::kQTileBytes;
-                            const uint32_t tb = opaque(tmem_base);
+                            constexpr uint32_t tb = tmem_base;
 #pragma unroll
                             for (int ks = 0; ks < DPAD / 16; ++ks)
                                 umma_ss(tb + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
@@ -617,6 +627,8 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     for (int i = 0; i < kNQ; ++i) s_step(w, i, w.j_lo, ring_addr + Cfg::kKVTileBytes);
                     commit(&kv_empty[0]);
                     ds = 1;
+                    mbar_wait(&kv_full[1 % Cfg::kDS], (1 / Cfg::kDS) & 1);   // the double slot of the first KV step
+                    tc_fence_after();
                 }
                 while (item >= 0) {
 #ifdef MFA_TRACE
@@ -624,13 +636,22 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
 #endif
                     PrefillItem wn;
                     int nitem = -1;
+                    bool looked = false;           // wn / nitem are valid
+                    bool early[2] = {false, false};   // the next item's first S of tile i has been issued already
                     for (int j = w.j_lo; j < w.n_max; ++j) {
                         const bool last = (j + 1 == w.n_max);
-                        if (last) nitem = next_work(item + (int)gridDim.x, wn);
+                        const bool penult = MFA_EARLY_S && (j + 2 == w.n_max);
+                        if ((last || penult) && !looked) {
+                            nitem = next_work(item + (int)gridDim.x, wn);
+                            looked = true;
+                        }
+                        // (this step's double slot was waited for in the MIDDLE of the previous step, right after Q tile 0's
+                        // batch of S MMAs, when ~4 SS instructions are still queued: at the loop boundary the tensor pipe
+                        // has only ~270 cycles of queued work, and a barrier wait there -- ~90 cycles even when the phase
+                        // completed long ago -- plus the commit and the first P wait left it idle for ~300 cycles per step)
                         const uint32_t st = ds % Cfg::kDS;
-                        mbar_wait(&kv_full[st], (ds / Cfg::kDS) & 1);
                         ++ds;
-                        tc_fence_after();
+                        const bool more = !last || nitem >= 0;   // another KV step follows (this item's or the next item's)
                         MFA_TR(2, j, 0);
                         const uint32_t va = opaque(ring_addr) + (2 * st) * Cfg::kKVTileBytes;
                         const uint32_t ka = va + Cfg::kKVTileBytes;
@@ -657,13 +678,31 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
 #endif
                             }
                             if (!last) s_step(w, i, j + 1, ka);
+                            if (i == 0 && more) {
+                                mbar_wait(&kv_full[ds % Cfg::kDS], (ds / Cfg::kDS) & 1);
+                                tc_fence_after();
+                            }
                             MFA_TR(2, j, 3 + 3 * i);
                         }
                         // the item's last step: both P.V first, then the next item's first S (its Q tiles may still be
                         // in flight; the wait must not hold back this item's P.V)
                         if (last && nitem >= 0) {
 #pragma unroll
-                            for (int i = 0; i < kNQ; ++i) s_step(wn, i, wn.j_lo, ka);
+                            for (int i = 0; i < kNQ; ++i)
+                                if (!early[i]) s_step(wn, i, wn.j_lo, ka);
+                        }
+                        // the step before: a tile that is already done with this item (no S(j+1), e.g. Q tile 0 under the
+                        // causal mask) takes the next item's first S now.  Its K tile is in the NEXT step's double slot,
+                        // which was waited for above; that slot's release (the next step's commit) covers this MMA too.
+                        if (penult && nitem >= 0) {
+                            const uint32_t ka_next = opaque(ring_addr) + (2 * (ds % Cfg::kDS) + 1) * Cfg::kKVTileBytes;
+#pragma unroll
+                            for (int i = 0; i < kNQ; ++i) {
+                                if (j + 1 >= w.n_i[i] && wn.active(i, wn.j_lo)) {
+                                    s_step(wn, i, wn.j_lo, ka_next);
+                                    early[i] = true;
+                                }
+                            }
                         }
                         commit(&kv_empty[st]);
                     }

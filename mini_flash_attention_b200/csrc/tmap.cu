@@ -23,8 +23,8 @@ EncodeTiledFn get_encode_fn() {
 }
 }  // namespace
 
-const char* encode_tmap_4d(CUtensorMap* out, const void* base, bool is_bf16, const uint64_t dims[4],
-                           const int64_t strides_elems[4], const uint32_t box[4], CUtensorMapSwizzle swizzle) {
+static const char* encode_impl(CUtensorMap* out, const void* base, CUtensorMapDataType dtype, int eb, const uint64_t dims[4],
+                               const int64_t strides_elems[4], const uint32_t box[4], CUtensorMapSwizzle swizzle) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return "cuTensorMapEncodeTiled entry point not available";
     if (reinterpret_cast<uintptr_t>(base) & 15) return "tensor base address must be 16-byte aligned for TMA";
@@ -40,17 +40,18 @@ const char* encode_tmap_4d(CUtensorMap* out, const void* base, bool is_bf16, con
         int64_t s = strides_elems[i];
         if (dims[i] <= 1) {
             // size-1 dimension: its stride is never applied, any legal value works; use the extent below it
-            s = (i == 1) ? static_cast<int64_t>(gdim[0]) : static_cast<int64_t>(gstride[i - 2] / 2 * gdim[i - 1]);
-            if (s % 8) s = (s + 7) / 8 * 8;
+            s = (i == 1) ? static_cast<int64_t>(gdim[0]) : static_cast<int64_t>(gstride[i - 2] / eb * gdim[i - 1]);
+            const int64_t q = 16 / eb;   // elements per 16 bytes
+            if (s % q) s = (s + q - 1) / q * q;
         } else if (s <= 0) {
             // a broadcast (expand()ed, stride 0) or reversed dimension of extent > 1: a tensor map cannot express it,
             // and inventing a stride would read the wrong rows -- the caller must materialise the tensor
             return "zero or negative stride on a dimension of extent > 1 (broadcast view): make the tensor contiguous";
         }
-        if ((s * 2) % 16) return "tensor strides must be multiples of 16 bytes for TMA";
-        gstride[i - 1] = static_cast<cuuint64_t>(s) * 2;
+        if ((s * eb) % 16) return "tensor strides must be multiples of 16 bytes for TMA";
+        gstride[i - 1] = static_cast<cuuint64_t>(s) * eb;
     }
-    CUresult r = fn(out, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
+    CUresult r = fn(out, dtype, 4,
                     const_cast<void*>(base), gdim, gstride, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -64,6 +65,17 @@ const char* encode_tmap_4d(CUtensorMap* out, const void* base, bool is_bf16, con
         return msg;
     }
     return nullptr;
+}
+
+const char* encode_tmap_4d(CUtensorMap* out, const void* base, bool is_bf16, const uint64_t dims[4],
+                           const int64_t strides_elems[4], const uint32_t box[4], CUtensorMapSwizzle swizzle) {
+    return encode_impl(out, base, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, dims,
+                       strides_elems, box, swizzle);
+}
+
+const char* encode_tmap_4d_u8(CUtensorMap* out, const void* base, const uint64_t dims[4], const int64_t strides_elems[4],
+                              const uint32_t box[4], CUtensorMapSwizzle swizzle) {
+    return encode_impl(out, base, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, dims, strides_elems, box, swizzle);
 }
 
 }  // namespace mfa

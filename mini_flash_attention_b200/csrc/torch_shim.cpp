@@ -39,8 +39,9 @@ void check_qkv(const at::Tensor& q, const at::Tensor& k, const at::Tensor& v) {
 bool tma_ok(const at::Tensor& t) {
     if (reinterpret_cast<uintptr_t>(t.data_ptr()) % 16) return false;
     // (a broadcast view -- expand(): stride 0 on an extent > 1 -- cannot be expressed by a tensor map either)
+    const int64_t per16 = 16 / (int64_t)t.element_size();   // elements per 16 bytes (8, or 16 for an e4m3 cache)
     for (int64_t d = 0; d + 1 < t.dim(); ++d)
-        if (t.stride(d) % 8 || (t.stride(d) <= 0 && t.size(d) > 1)) return false;
+        if (t.stride(d) % per16 || (t.stride(d) <= 0 && t.size(d) > 1)) return false;
     return t.dim() == 0 || t.stride(t.dim() - 1) == 1;
 }
 at::Tensor tma_ready(const at::Tensor& t) { return tma_ok(t) ? t : t.contiguous(); }
@@ -250,8 +251,21 @@ struct DecodeCall {
 
 void decode_params(DecodeCall& c, const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache,
                    const std::optional<at::Tensor>& cache_seqlens, const std::optional<at::Tensor>& block_table,
-                   int64_t num_splits) {
-    check_qkv(q, k_cache, v_cache);
+                   int64_t num_splits, bool fp8 = false) {
+    if (fp8) {
+        // e4m3 cache (the reference gates the dtype at api.cpp:126-129): q keeps its 16-bit type
+        TORCH_CHECK(q.scalar_type() == at::kHalf || q.scalar_type() == at::kBFloat16,
+                    "FlashAttention only support fp16 and bf16 data type");
+        TORCH_CHECK(k_cache.scalar_type() == at::kFloat8_e4m3fn && v_cache.scalar_type() == at::kFloat8_e4m3fn,
+                    "k_cache and v_cache must both be torch.float8_e4m3fn");
+        TORCH_CHECK(q.is_cuda() && k_cache.is_cuda() && v_cache.is_cuda(), "q, k_cache and v_cache must be on CUDA");
+        TORCH_CHECK(q.dim() >= 1 && q.stride(-1) == 1 && k_cache.dim() >= 1 && k_cache.stride(-1) == 1 &&
+                        v_cache.dim() >= 1 && v_cache.stride(-1) == 1,
+                    "Input tensor must have contiguous last dimension");
+        TORCH_CHECK(q.size(-1) % 128 == 0, "an e4m3 KV cache needs head_dim to be a multiple of 128");
+    } else {
+        check_qkv(q, k_cache, v_cache);
+    }
     TORCH_CHECK(q.dim() == 4, "q must have shape (batch, 1, num_heads, head_dim)");
     const int64_t batch = q.size(0), seqlen_q = q.size(1), heads = q.size(2), head_dim = q.size(3);
     TORCH_CHECK(seqlen_q == 1, "flash decoding expects seqlen_q == 1, got ", seqlen_q);   // api.cpp:377
@@ -394,6 +408,55 @@ std::tuple<at::Tensor, at::Tensor> mini_flash_attention_with_kvcache_lse(
     std::optional<at::Tensor> block_table, bool /*causal*/, int64_t num_splits) {
     return kvcache_impl(q, k_cache, v_cache, cache_seqlens, block_table, num_splits, true);
 }
+// decode over an e4m3 KV cache; k_scale / v_scale: optional (kv_heads,) fp32 device tensors (the Python side expands
+// floats and per-tensor scales)
+std::tuple<at::Tensor, std::optional<at::Tensor>> mini_flash_attention_with_kvcache_fp8(
+    const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache, std::optional<at::Tensor> cache_seqlens,
+    std::optional<at::Tensor> block_table, int64_t num_splits, bool return_lse, int64_t window_left,
+    std::optional<at::Tensor> k_scale, std::optional<at::Tensor> v_scale) {
+    DecodeCall c;
+    decode_params(c, q, k_cache, v_cache, cache_seqlens, block_table, num_splits, true);
+    at::Tensor ks, vs;
+    c.P.kv_fp8 = 1;
+    c.P.kv_scale_stride = 1;
+    if (k_scale.has_value()) {
+        TORCH_CHECK(k_scale->is_cuda() && k_scale->scalar_type() == at::kFloat && k_scale->numel() == c.P.kv_heads, "k_scale must be a (kv_num_heads,) fp32 CUDA tensor");
+        ks = k_scale->contiguous();
+        c.P.k_scale_ptr = ks.data_ptr<float>();
+    }
+    if (v_scale.has_value()) {
+        TORCH_CHECK(v_scale->is_cuda() && v_scale->scalar_type() == at::kFloat && v_scale->numel() == c.P.kv_heads, "v_scale must be a (kv_num_heads,) fp32 CUDA tensor");
+        vs = v_scale->contiguous();
+        c.P.v_scale_ptr = vs.data_ptr<float>();
+    }
+    if (window_left >= 0) {
+        c.P.local_window = 1;
+        c.P.window_size_left = (int32_t)window_left;
+        c.P.window_size_right = -1;
+    }
+    c10::cuda::CUDAGuard guard(q.device());
+    at::Tensor out = at::empty_like(q);
+    at::Tensor lse;
+    if (return_lse) lse = at::empty({q.size(0), q.size(2), 1}, q.options().dtype(at::kFloat));
+    auto ret = [&]() -> std::tuple<at::Tensor, std::optional<at::Tensor>> {
+        return {out, return_lse ? std::optional<at::Tensor>(lse) : std::nullopt};
+    };
+    if (q.numel() == 0) return ret();
+    if (c.P.seqlen_k == 0) {
+        if (return_lse) lse.fill_(-std::numeric_limits<float>::infinity());
+        out.zero_();
+        return ret();
+    }
+    const bool o_ok = reinterpret_cast<uintptr_t>(out.data_ptr()) % 8 == 0 && out.stride(0) % 4 == 0 && out.stride(2) % 4 == 0;
+    at::Tensor oc = o_ok ? out : at::empty(out.sizes(), out.options());
+    c.P.o_ptr = oc.data_ptr();
+    c.P.o_batch_stride = oc.stride(0); c.P.o_row_stride = oc.stride(1); c.P.o_head_stride = oc.stride(2);
+    if (return_lse) c.P.softmax_lse_ptr = lse.data_ptr<float>();
+    run_decode(c.P, q);
+    if (!oc.is_same(out)) out.copy_(oc);
+    return ret();
+}
+
 std::tuple<at::Tensor, std::optional<at::Tensor>> mini_flash_attention_with_kvcache_ext(
     const at::Tensor& q, const at::Tensor& k_cache, const at::Tensor& v_cache, std::optional<at::Tensor> cache_seqlens,
     std::optional<at::Tensor> block_table, bool /*causal*/, int64_t num_splits, bool return_lse,
@@ -476,6 +539,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("mini_flash_attention_with_kvcache_ext", &mini_flash_attention_with_kvcache_ext, py::arg("q"),
           py::arg("k_cache"), py::arg("v_cache"), py::arg("cache_seqlens"), py::arg("block_table"), py::arg("causal"),
           py::arg("num_splits"), py::arg("return_lse"), py::arg("k_new"), py::arg("v_new"), py::arg("window_left") = -1);
+    m.def("mini_flash_attention_with_kvcache_fp8", &mini_flash_attention_with_kvcache_fp8, py::arg("q"), py::arg("k_cache"),
+          py::arg("v_cache"), py::arg("cache_seqlens"), py::arg("block_table"), py::arg("num_splits"), py::arg("return_lse"),
+          py::arg("window_left"), py::arg("k_scale"), py::arg("v_scale"));
     m.def("decode_kv_sharded_fused", &decode_kv_sharded_fused, py::arg("q"), py::arg("k_cache"), py::arg("v_cache"),
           py::arg("cache_seqlens"), py::arg("block_table"), py::arg("num_splits"), py::arg("xchg"));
     m.def("decode_partial", &decode_partial, py::arg("q"), py::arg("k_cache"), py::arg("v_cache"),

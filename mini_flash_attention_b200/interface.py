@@ -118,6 +118,8 @@ def flash_attn_with_kvcache(
     k: Optional[torch.Tensor] = None,
     v: Optional[torch.Tensor] = None,
     window_size: Tuple[int, int] = (-1, -1),
+    k_scale: Optional[Union[float, torch.Tensor]] = None,
+    v_scale: Optional[Union[float, torch.Tensor]] = None,
 ):
     """Single-token decode against a KV cache (reference: interface.py:95-124).
 
@@ -138,9 +140,19 @@ def flash_attn_with_kvcache(
             window are not read, so the step costs O(window), not O(cache_seqlens).  -1 = unbounded.
         return_lse: (new) also return softmax_lse (batch_size, nheads, 1) fp32 -- the tensor the reference allocates
             and drops (api.cpp:436-437)
+        k_scale, v_scale: (new -- SURVEY 8f row 4) for a cache stored as torch.float8_e4m3fn (half the bytes per key; q
+            and the output stay fp16/bf16): dequantisation scales, a float / 1-element tensor (per tensor) or a
+            (nheads_k,) fp32 tensor (per KV head); the key is k_cache * k_scale, the value v_cache * v_scale.
+            None = 1.  head_dim must be a multiple of 128.  Not combinable with k= / v= (append).
     """
     assert q.size(1) == 1, "flash_attn_with_kvcache currently only supports seqlen_q=1 for decoding"
     wl, _ = _window(window_size)
+    if k_cache.dtype not in (torch.float16, torch.bfloat16):   # e4m3 cache
+        assert k is None and v is None, "appending k/v into an e4m3 cache is not supported"
+        out, lse = _C.mini_flash_attention_with_kvcache_fp8(q, k_cache, v_cache, cache_seqlens, block_table, num_splits,
+                                                            return_lse, wl, k_scale, v_scale)
+        return (out, lse) if return_lse else out
+    assert k_scale is None and v_scale is None, "k_scale / v_scale are for an e4m3 (torch.float8_e4m3fn) cache"
     if k is not None or v is not None or wl >= 0:
         out, lse = _C.mini_flash_attention_with_kvcache_ext(q, k_cache, v_cache, cache_seqlens, block_table, causal,
                                                             num_splits, return_lse, k, v, wl)

@@ -83,6 +83,16 @@ def lse_ref(q, k, causal: bool = False, bottom_right: bool = False, window_size=
     return torch.logsumexp(s, dim=-1)
 
 
+def dequant_e4m3(cache: torch.Tensor, scale=None) -> torch.Tensor:
+    """e4m3 KV cache -> fp32 values: byte value * scale, scale a float, a 1-element tensor or a
+    (kv_heads,) tensor applied along the head axis (dim -2).  The oracle of the e4m3 decode is dequantise-then-fp32."""
+    x = cache.float()
+    if scale is None:
+        return x
+    s = torch.as_tensor(scale, dtype=torch.float32, device=x.device).reshape(-1)
+    return x * (s.view(-1, 1) if s.numel() > 1 else s)
+
+
 def gather_paged(cache: torch.Tensor, block_table_row: torch.Tensor, length: int) -> torch.Tensor:
     """cache (num_blocks, page, Hkv, D) -> the first `length` logical rows (length, Hkv, D), gathered per row."""
     page = cache.shape[1]

@@ -25,7 +25,7 @@ def test_library_exports_every_header_symbol(mfa_lib):
     for s in syms:
         assert hasattr(mfa_lib, s), f"{s} declared in include/mfa_b200.h but not exported"
     assert sorted(_lib.EXPORTS) == syms
-    assert mfa_lib.mfa_abi_version() == 3
+    assert mfa_lib.mfa_abi_version() == 4
 
 
 def test_params_struct_matches_header_layout(mfa_lib):
@@ -41,6 +41,7 @@ int main(void) {
   printf("%zu %zu %zu %zu %zu %zu\n", sizeof(mfa_params_t), offsetof(mfa_params_t, is_causal),
          offsetof(mfa_params_t, softmax_scale), offsetof(mfa_params_t, cu_seqlens_q),
          offsetof(mfa_params_t, k_cache_block_stride), offsetof(mfa_params_t, partial_out));
+  printf("%zu %zu %zu\n", offsetof(mfa_params_t, kv_fp8), offsetof(mfa_params_t, k_scale_ptr), offsetof(mfa_params_t, v_scale_ptr));
   printf("%zu %zu %zu %zu %zu %zu\n", offsetof(mfa_params_t, local_window), offsetof(mfa_params_t, causal_bottom_right), sizeof(mfa_append_params_t),
          offsetof(mfa_append_params_t, k_cache), offsetof(mfa_append_params_t, seqlens_out),
          offsetof(mfa_append_params_t, is_bf16));
@@ -55,6 +56,7 @@ int main(void) {
     from mini_flash_attention_b200._lib import MfaAppendParams as A
     assert vals == [ctypes.sizeof(MfaParams), MfaParams.is_causal.offset, MfaParams.softmax_scale.offset,
                     MfaParams.cu_seqlens_q.offset, MfaParams.k_cache_block_stride.offset, MfaParams.partial_out.offset,
+                    MfaParams.kv_fp8.offset, MfaParams.k_scale_ptr.offset, MfaParams.v_scale_ptr.offset,
                     MfaParams.local_window.offset, MfaParams.causal_bottom_right.offset, ctypes.sizeof(A), A.k_cache.offset, A.seqlens_out.offset,
                     A.is_bf16.offset]
 
@@ -78,7 +80,7 @@ def test_python_surface_matches_reference():
     sig = inspect.signature(m.flash_attn_with_kvcache)
     assert positional(m.flash_attn_with_kvcache) == ["q", "k_cache", "v_cache", "cache_seqlens", "block_table", "num_splits"]
     assert kw_only(m.flash_attn_with_kvcache) == {"causal": False, "return_lse": False, "k": None, "v": None,
-                                                     "window_size": (-1, -1)}
+                                                     "window_size": (-1, -1), "k_scale": None, "v_scale": None}
     assert sig.parameters["num_splits"].default == 0
     for name in ("mini_flash_attention_forward", "mini_flash_attention_varlen_forward", "mini_flash_attention_with_kvcache"):
         assert hasattr(m._C, name)

@@ -123,10 +123,12 @@ def test_persistent_grid_one_tile_items(mfa):
 
 
 def test_many_short_items_back_to_back(mfa):
-    """S = 256 ... 384 at B*H >> #SMs: every CTA crosses many item boundaries (the K/V stream runs across items)."""
+    """S = 256 ... 384 at B*H >> #SMs: every CTA crosses many item boundaries (the K/V stream runs across items).
+    (V is scaled by 1/2: with 19 M standard-normal values |v| reaches 5.5, and the first causal rows copy V almost
+    verbatim -- the bf16 rounding of such an OUTPUT alone is 2^-7 = 0.0078 of the 1e-2 budget.)"""
     from oracle import ref_attention as R
     for S in (256, 257, 384):
-        q, k, v = _r((16, S, 24, 128), torch.bfloat16, S), _r((16, S, 24, 128), torch.bfloat16, S + 1), _r((16, S, 24, 128), torch.bfloat16, S + 2)
+        q, k, v = _r((16, S, 24, 128), torch.bfloat16, S), _r((16, S, 24, 128), torch.bfloat16, S + 1), _r((16, S, 24, 128), torch.bfloat16, S + 2) * 0.5
         for causal in (False, True):
             out = mfa.flash_attn_func(q, k, v, causal=causal)
             assert (out.float() - R.attention_ref(q, k, v, causal)).abs().max().item() <= TOL["bf16"]
