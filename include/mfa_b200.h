@@ -210,10 +210,6 @@ int    mfa_decode_fwd_kv_sharded(const mfa_params_t* p, void* workspace, size_t 
 /* tuning aid: libraries built with -DMFA_TRACE write clock64() stamps of prefill CTA (0,0,0) into this device
  * buffer ([3 roles][64 iterations][8 events] int64); a no-op in normal builds.  NULL disables. */
 void mfa_debug_set_trace(void* device_buffer);
-/* Kernel choice for head_dim in (64, 128]: 0 = single-CTA kernel (default), 1 = CTA-pair kernel (cta_group::2).
- * Also settable at load time with MFA_PREFILL_IMPL=pair.  Both are parity-tested; tuning aid. */
-void mfa_debug_set_prefill_impl(int impl);
-
 /* number of kernel launches issued by this library since load (bench.py reports it) */
 uint64_t mfa_launch_count(void);
 

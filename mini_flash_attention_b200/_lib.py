@@ -67,7 +67,7 @@ class MfaAppendParams(ctypes.Structure):
 EXPORTS = (
     "mfa_abi_version", "mfa_last_error", "mfa_device_supported", "mfa_prefill_fwd", "mfa_decode_num_splits",
     "mfa_decode_workspace_bytes", "mfa_decode_fwd", "mfa_combine_partials", "mfa_launch_count", "mfa_selftest_umma",
-    "mfa_debug_set_trace", "mfa_selftest_umma2", "mfa_debug_set_prefill_impl", "mfa_kvcache_append",
+    "mfa_debug_set_trace", "mfa_selftest_umma2", "mfa_kvcache_append",
     "mfa_xchg_create", "mfa_xchg_export", "mfa_xchg_connect", "mfa_xchg_connect_ptrs", "mfa_xchg_local_ptr",
     "mfa_xchg_status", "mfa_xchg_clear_status", "mfa_xchg_destroy", "mfa_decode_kv_sharded_workspace_bytes", "mfa_decode_fwd_kv_sharded",
 )
@@ -130,8 +130,6 @@ def load() -> ctypes.CDLL:
     lib.mfa_decode_fwd_kv_sharded.restype = ctypes.c_int
     lib.mfa_debug_set_trace.argtypes = [ctypes.c_void_p]
     lib.mfa_debug_set_trace.restype = None
-    lib.mfa_debug_set_prefill_impl.argtypes = [ctypes.c_int]
-    lib.mfa_debug_set_prefill_impl.restype = None
     lib.mfa_selftest_umma.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                       ctypes.c_int, ctypes.c_int, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]
     lib.mfa_selftest_umma.restype = ctypes.c_int

@@ -19,7 +19,7 @@ REPO = os.path.dirname(PKG_DIR)
 LIB_PATH = os.path.join(PKG_DIR, "libmfa_b200.so")
 OBJ_DIR = os.path.join(PKG_DIR, "_obj")
 
-SOURCES = ["capi.cu", "tmap.cu", "decode_sm100.cu", "prefill_sm100.cu", "prefill_pair_sm100.cu", "selftest_sm100.cu", "selftest2_sm100.cu", "kvcache_append_sm100.cu", "xchg_sm100.cu"]
+SOURCES = ["capi.cu", "tmap.cu", "decode_sm100.cu", "prefill_sm100.cu", "selftest_sm100.cu", "selftest2_sm100.cu", "kvcache_append_sm100.cu", "xchg_sm100.cu"]
 HEADERS = ["kparams.h", "ptx.cuh", "tmap.h", "merge.cuh", os.path.join(REPO, "include", "mfa_b200.h")]
 
 NVCC_FLAGS = [

@@ -24,8 +24,6 @@ cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t s
 cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                            const PrefillKParams& p, bool is_bf16, int dpad, cudaStream_t stream);
 int prefill_rows_per_cta(int dpad);
-cudaError_t launch_prefill_pair(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
-                                const PrefillKParams& p, bool is_bf16, cudaStream_t stream);
 cudaError_t launch_kvcache_append(const mfa_append_params_t& p, int sm_count, cudaStream_t stream);
 cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream);
 }  // namespace mfa
@@ -46,11 +44,6 @@ namespace {
 
 thread_local char g_err[512] = "";
 long long* g_trace = nullptr;   // tuning aid, see mfa_debug_set_trace
-static int initial_prefill_impl() {
-    const char* e = getenv("MFA_PREFILL_IMPL");
-    return (e && strcmp(e, "pair") == 0) ? 1 : 0;
-}
-std::atomic<int> g_prefill_impl{initial_prefill_impl()};   // 0 = single-CTA kernel, 1 = CTA-pair kernel (head_dim in (64,128])
 std::atomic<uint64_t> g_launches{0};
 
 int fail(int code, const char* fmt, ...) {
@@ -124,7 +117,6 @@ extern "C" {
 
 int mfa_abi_version(void) { return MFA_B200_ABI_VERSION; }
 void mfa_debug_set_trace(void* device_buffer) { g_trace = static_cast<long long*>(device_buffer); }
-void mfa_debug_set_prefill_impl(int impl) { g_prefill_impl.store(impl == 1 ? 1 : 0); }
 const char* mfa_last_error(void) { return g_err; }
 uint64_t mfa_launch_count(void) { return g_launches.load(); }
 
@@ -158,12 +150,8 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     const int dpad = dpad_of(D);
     const bool bf16 = p->is_bf16 != 0;
 
-    // head_dim in (64, 128] has two kernels: the single-CTA one (prefill_sm100.cu, default: faster today) and the
-    // CTA-pair one (prefill_pair_sm100.cu; MFA_PREFILL_IMPL=pair or mfa_debug_set_prefill_impl(1) selects it).
-    // (the opt-in pair kernel implements the reference's top-left mask only)
     const bool window = p->local_window && (p->window_size_left >= 0 || p->window_size_right >= 0);
-    const bool use_pair = (dpad == 128) && (g_prefill_impl.load() == 1) && !(p->is_causal && p->causal_bottom_right) && !window;
-    const int kv_tile_box = use_pair ? 64 : mfa::kPrefillBlockN;
+    const int kv_tile_box = mfa::kPrefillBlockN;
 
     CUtensorMap tmQ, tmK, tmV;
     const char* err;
@@ -241,8 +229,7 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     kp.lse_head_stride = varlen ? (int64_t)p->total_q : (int64_t)p->seqlen_q;
     kp.trace = g_trace;
 
-    cudaError_t e = use_pair ? mfa::launch_prefill_pair(tmQ, tmK, tmV, kp, bf16, static_cast<cudaStream_t>(cuda_stream))
-                             : mfa::launch_prefill(tmQ, tmK, tmV, kp, bf16, dpad, static_cast<cudaStream_t>(cuda_stream));
+    cudaError_t e = mfa::launch_prefill(tmQ, tmK, tmV, kp, bf16, dpad, static_cast<cudaStream_t>(cuda_stream));
     if (e != cudaSuccess) return cuda_fail(e, "prefill launch");
     g_launches.fetch_add(1);
     return MFA_OK;

@@ -18,6 +18,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
+#include <cstdlib>
 #include <type_traits>
 
 #include "kparams.h"
@@ -111,8 +112,10 @@ struct DecodeCfg {
     static constexpr int kStageBytes = 2 * kTileBytes;           // K then V
     static constexpr int kStages = (DPAD * kEB == 128) ? 2 * MFA_DECODE_STAGES : MFA_DECODE_STAGES;   // >= 32 KB per stage pair
     static constexpr int kRingBytes = kStages * kStageBytes;
-    static constexpr int kMergeBytes = 4 * 16 * DPAD * 4 + 512;  // cross-warp merge staging (aliases the ring)
-    static constexpr int kBarOffset = kRingBytes > kMergeBytes ? kRingBytes : kMergeBytes;
+    // cross-warp merge staging.  It has its own shared memory (not the ring's): the CTA is persistent, and while the
+    // consumers merge item n the producer warp is already filling the ring with the first tiles of item n + 1
+    static constexpr int kMergeBytes = 4 * 16 * DPAD * 4 + 512;
+    static constexpr int kBarOffset = kRingBytes + kMergeBytes;
     static constexpr int kSmemBytes = kBarOffset + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -147,26 +150,39 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kBarOffset);
     uint64_t* empty_bar = full_bar + kStages;
 
-    const int split = blockIdx.x;
-    const int kh = blockIdx.y / p.head_tiles;
-    const int htile = blockIdx.y % p.head_tiles;
-    const int b = blockIdx.z;
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    const int len = p.seqlens_k ? min(p.seqlens_k[b], p.seqlen_k) : p.seqlen_k;
-    const int n_blocks = (len + kTile - 1) / kTile;
-    // sliding window: the single query sits at position len - 1 and sees keys [first_key, len); tiles in
-    // front of the window are not loaded and the splits partition only the tiles of the window
-    const int first_key = (p.window_left >= 0) ? max(len - 1 - p.window_left, 0) : 0;
-    const int tile_lo = first_key / kTile;
-    const int per_split = (n_blocks - tile_lo + p.num_splits - 1) / p.num_splits;   // decode.cuh:27
-    const int t0 = tile_lo + split * per_split;
-    const int t1 = min(n_blocks, t0 + per_split);
-    const int ntiles = max(t1 - t0, 0);
-
-    const int gvalid = min(p.group - htile * kDecodeMaxGroup, kDecodeMaxGroup);   // q heads served by this CTA
-    const int head0 = kh * p.group + htile * kDecodeMaxGroup;
+    // PERSISTENT: the grid is (resident CTAs per SM) x (SMs), or one CTA per work item when there are fewer items.  A work
+    // item is (split, KV head x head tile, batch) -- what used to be one CTA -- and every CTA walks the items blockIdx.x,
+    // blockIdx.x + gridDim.x, ... with both of its roles in the same order.  The barriers and the ring live across
+    // items (phases come from a running tile counter), so the producer streams the next item's first tiles while the
+    // consumers are still merging the current one: the ~3 us ramp of a fresh CTA (barrier init, tensor-map fetch, first
+    // HBM round trip) is paid once per CTA instead of once per item -- a third of the kernel at KV = 512.
+    struct Item {
+        int split, kh, htile, b, len, first_key, t0, ntiles;
+    };
+    const int ny = p.kv_heads * p.head_tiles;
+    const int total_items = p.num_splits * ny * p.batch;
+    auto get_item = [&](int item) {
+        Item w;
+        w.split = item % p.num_splits;
+        const int rest = item / p.num_splits;
+        const int y = rest % ny;
+        w.b = rest / ny;
+        w.kh = y / p.head_tiles;
+        w.htile = y % p.head_tiles;
+        w.len = p.seqlens_k ? min(p.seqlens_k[w.b], p.seqlen_k) : p.seqlen_k;
+        const int n_blocks = (w.len + kTile - 1) / kTile;
+        // sliding window: the single query sits at position len - 1 and sees keys [first_key, len);
+        // tiles in front of the window are not loaded and the splits partition only the tiles of the window
+        w.first_key = (p.window_left >= 0) ? max(w.len - 1 - p.window_left, 0) : 0;
+        const int tile_lo = w.first_key / kTile;
+        const int per_split = (n_blocks - tile_lo + p.num_splits - 1) / p.num_splits;   // decode.cuh:27
+        w.t0 = tile_lo + w.split * per_split;
+        w.ntiles = max(min(n_blocks, w.t0 + per_split) - w.t0, 0);
+        return w;
+    };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
@@ -179,38 +195,42 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
 
     if (warp == 4) {
         // ------------------------------------------------------------ TMA producer
-        if (lane == 0 && ntiles > 0) {
+        if (lane == 0) {
             prefetch_tensormap(&tmK);
             prefetch_tensormap(&tmV);
-            const int32_t* bt = p.block_table ? p.block_table + (int64_t)b * p.block_table_batch_stride : nullptr;
-            const int chunk_bytes = p.box_rows * 128;   // one box = box_rows x 64 elements
-            for (int it = 0; it < ntiles; ++it) {
-                const int s = it % kStages;
-                const uint32_t ph = (it / kStages) & 1;
-                mbar_wait(&empty_bar[s], ph ^ 1);
-                const int row0 = (t0 + it) * kTile;
-                const int rows_valid = min(len - row0, kTile);
-                const int nchunks = (rows_valid + p.box_rows - 1) / p.box_rows;
-                mbar_arrive_expect_tx(&full_bar[s], static_cast<uint32_t>(nchunks * chunk_bytes * kSub * 2));
-                uint8_t* kdst = smem + s * Cfg::kStageBytes;
-                uint8_t* vdst = kdst + Cfg::kTileBytes;
-                for (int c = 0; c < nchunks; ++c) {
-                    const int row = row0 + c * p.box_rows;
-                    int blk, in_page;
-                    if (bt) {
-                        const int pg = row / p.page;
-                        in_page = row - pg * p.page;
-                        blk = bt[pg];
-                    } else {
-                        in_page = row;
-                        blk = b;
-                    }
+            const int chunk_bytes = p.box_rows * 128;   // one box = box_rows x 128 bytes
+            int it = 0;   // ring position, runs across items
+            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+                const Item w = get_item(item);
+                const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
+                for (int t = 0; t < w.ntiles; ++t, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    const int row0 = (w.t0 + t) * kTile;
+                    const int rows_valid = min(w.len - row0, kTile);
+                    const int nchunks = (rows_valid + p.box_rows - 1) / p.box_rows;
+                    mbar_arrive_expect_tx(&full_bar[s], static_cast<uint32_t>(nchunks * chunk_bytes * kSub * 2));
+                    uint8_t* kdst = smem + s * Cfg::kStageBytes;
+                    uint8_t* vdst = kdst + Cfg::kTileBytes;
+                    for (int c = 0; c < nchunks; ++c) {
+                        const int row = row0 + c * p.box_rows;
+                        int blk, in_page;
+                        if (bt) {
+                            const int pg = row / p.page;
+                            in_page = row - pg * p.page;
+                            blk = bt[pg];
+                        } else {
+                            in_page = row;
+                            blk = w.b;
+                        }
 #pragma unroll
-                    for (int hf = 0; hf < kSub; ++hf) {
-                        tma_load_4d(kdst + hf * (kTile * 128) + c * chunk_bytes, &tmK, &full_bar[s], hf * Cfg::kBoxElems,
-                                    in_page, kh, blk);
-                        tma_load_4d(vdst + hf * (kTile * 128) + c * chunk_bytes, &tmV, &full_bar[s], hf * Cfg::kBoxElems,
-                                    in_page, kh, blk);
+                        for (int hf = 0; hf < kSub; ++hf) {
+                            tma_load_4d(kdst + hf * (kTile * 128) + c * chunk_bytes, &tmK, &full_bar[s], hf * Cfg::kBoxElems,
+                                        in_page, w.kh, blk);
+                            tma_load_4d(vdst + hf * (kTile * 128) + c * chunk_bytes, &tmV, &full_bar[s], hf * Cfg::kBoxElems,
+                                        in_page, w.kh, blk);
+                        }
                     }
                 }
             }
@@ -219,10 +239,20 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
     }
 
     // ---------------------------------------------------------------- consumers (warps 0..3)
-    const T* qbase = static_cast<const T*>(p.q) + (int64_t)b * p.q_batch_stride;
     const int g0 = lane >> 2;        // head row of c0,c1 / a0,a2
     const int g1 = g0 + 8;           // head row of c2,c3 / a1,a3
     const int tq = lane & 3;
+    const int wrow = warp * 16;   // this warp's rows inside each tile
+    float* stage_o = reinterpret_cast<float*>(smem + Cfg::kRingBytes);                    // [4 warps][16 heads][DPAD]
+    float* stage_m = reinterpret_cast<float*>(smem + Cfg::kRingBytes + 4 * 16 * DPAD * 4);  // [4][16]
+    float* stage_l = stage_m + 64;
+    int it = 0;   // ring position, runs across items
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+    const Item w = get_item(item);
+    const int split = w.split, kh = w.kh, b = w.b, len = w.len, first_key = w.first_key, t0 = w.t0, ntiles = w.ntiles;
+    const int gvalid = min(p.group - w.htile * kDecodeMaxGroup, kDecodeMaxGroup);   // q heads served by this item
+    const int head0 = kh * p.group + w.htile * kDecodeMaxGroup;
+    const T* qbase = static_cast<const T*>(p.q) + (int64_t)b * p.q_batch_stride;
 
     uint32_t qa[KS][4];
 #pragma unroll
@@ -255,15 +285,14 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
     const float k_descale = (KV8 && p.k_scale) ? p.k_scale[kh * p.kv_scale_stride] : 1.f;
     const float v_descale = (KV8 && p.v_scale) ? p.v_scale[kh * p.kv_scale_stride] : 1.f;
     const float c2 = p.scale_log2 * k_descale;
-    const int wrow = warp * 16;   // this warp's rows inside each tile
 
-    for (int it = 0; it < ntiles; ++it) {
+    for (int t = 0; t < ntiles; ++t, ++it) {
         const int s = it % kStages;
         const uint32_t ph = (it / kStages) & 1;
         mbar_wait(&full_bar[s], ph);
         const uint32_t kaddr = smem_u32(smem + s * Cfg::kStageBytes);
         const uint32_t vaddr = kaddr + Cfg::kTileBytes;
-        const int row0 = (t0 + it) * kTile;
+        const int row0 = (t0 + t) * kTile;
         const int rows_valid = len - row0;   // >= 1
 
         if (rows_valid < wrow + 16) {
@@ -406,10 +435,7 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
 
-    named_bar_sync(1, 128);   // every consumer is done reading the ring; all issued TMA has landed
-    float* stage_o = reinterpret_cast<float*>(smem);                    // [4 warps][16 heads][DPAD]
-    float* stage_m = reinterpret_cast<float*>(smem + 4 * 16 * DPAD * 4);  // [4][16]
-    float* stage_l = stage_m + 64;
+    named_bar_sync(1, 128);   // every consumer has finished reading the staging area of the previous item
     if (tq == 0) {
         stage_m[warp * 16 + g0] = m0;
         stage_m[warp * 16 + g1] = m1;
@@ -493,6 +519,7 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
             }
         }
     }
+    }   // items
 }
 
 // LSE merge of `num_splits` normalised partials (decode.cuh:665-755 restated with a max-subtracted
@@ -546,7 +573,18 @@ static cudaError_t launch_decode_t(const CUtensorMap& tmK, const CUtensorMap& tm
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
-    dim3 grid(p.num_splits, p.kv_heads * p.head_tiles, p.batch);
+    static int slots[64] = {};        // resident CTAs per SM x SMs, per (T, DPAD, KV8) instantiation and device
+    if (dev < 64 && slots[dev] == 0) {
+        int per_sm = 0, sms = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kDecodeThreads, Cfg::kSmemBytes) != cudaSuccess || per_sm < 1) per_sm = 1;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 148;
+        slots[dev] = per_sm * sms;
+    }
+    const long long items = (long long)p.num_splits * p.kv_heads * p.head_tiles * p.batch;
+    if (items <= 0 || items > 0x7fffffffLL) return cudaErrorInvalidValue;
+    static const bool non_persistent = [] { const char* e = getenv("MFA_DECODE_NONPERSISTENT"); return e && e[0] == '1'; }();
+    const long long cap = (dev < 64 && slots[dev] > 0 && !non_persistent) ? slots[dev] : items;
+    dim3 grid((unsigned)(items < cap ? items : cap), 1, 1);
     kern<<<grid, kDecodeThreads, Cfg::kSmemBytes, stream>>>(tmK, tmV, p);
     return cudaGetLastError();
 }

@@ -71,7 +71,7 @@ constexpr int kPrefillBlockN = 128;   // KV rows per tile
 constexpr int kPrefillThreads = 384;  // 2 softmax warpgroups + 1 warpgroup {TMA warp, MMA warp, 2 spare}
 
 struct PrefillKParams {
-    const void* q;                 // pair kernel: Q rows are read directly (staged into TMEM), no tensor map
+    const void* q;                 // (Q goes through its tensor map; kept for diagnostics)
     int64_t q_batch_stride, q_head_stride, q_row_stride;
     void* o;
     int64_t o_batch_stride, o_head_stride, o_row_stride;

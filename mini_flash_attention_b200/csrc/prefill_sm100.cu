@@ -44,25 +44,12 @@
 #ifndef MFA_REG_HELPER
 #define MFA_REG_HELPER 72
 #endif
-// P hand-off from the softmax threads to the MMA warp.  MFA_PSPLIT 1: in two halves (p_lo after KV rows 0-63, p_hi after
-// 64-127) so that the first P.V k-steps run while the second half is exponentiated; 0: one hand-off per tile (one wait
-// and one tcgen05.wait::st / fence / arrive per thread less).  MFA_PARRIVE_WARP 1: one arrival per WARP (lane 0 after
-// __syncwarp; barrier count 4) instead of one per thread (count 128).
-#ifndef MFA_PSPLIT
-#define MFA_PSPLIT 1
+// MFA_SPEC_EXP 1: the first half of P is exponentiated with the stale running max while the row max is still being
+// computed (see the softmax warps); 0: max first, then the exponentials (round-1 order; tuning aid).
+#ifndef MFA_SPEC_EXP
+#define MFA_SPEC_EXP 1
 #endif
-// MFA_EARLY_S 1 (flat stream): a Q tile that finishes an item one KV step before the other (the causal mask: tile 0 has
-// one KV tile less than tile 1) gets the NEXT item's first S in that step already, so its softmax warpgroup works
-// through the other tile's lone last step instead of idling.
-#ifndef MFA_EARLY_S
-#define MFA_EARLY_S 1
-#endif
-#ifndef MFA_PARRIVE_WARP
-#define MFA_PARRIVE_WARP 0
-#endif
-#ifndef MFA_POLY_MASK
-#define MFA_POLY_MASK 0x8u   // pair 3 of every 4 -> a quarter of the exponentials off the MUFU (measured best)
-#endif
+
 
 #ifdef MFA_TRACE
 #define MFA_TR(role, it, ev)                                                                              \
@@ -109,16 +96,6 @@ struct PrefillCfg {
 #define MFA_STAGES128 4
 #endif
     static constexpr int kStages = (DPAD == 64) ? 8 : (DPAD == 128 ? MFA_STAGES128 : 2);
-    // Flat K/V stream (kStages >= 4): the ring is used as kStages/2 DOUBLE SLOTS [V_j | K_{j+1}] with one full and one
-    // empty barrier each -- the two tiles one KV step of the MMA warp needs arrive under one barrier, and the stream
-    // runs across work items ([V_last(item a) | K_first(item a+1)]).  head_dim 256 has room for 2 slots only and keeps
-    // the per-tile ring.
-#ifdef MFA_NO_FLAT
-    static constexpr bool kFlat = false;   // tuning aid: the per-tile ring of round 1 at every head_dim
-#else
-    static constexpr bool kFlat = kStages >= 4;
-#endif
-    static constexpr int kDS = kStages / 2;
     static constexpr int kQBytes = kNQ * kQTileBytes;
     static constexpr int kRingBytes = kStages * kKVTileBytes;
     static constexpr int kBarOffset = kQBytes + kRingBytes;
@@ -127,7 +104,6 @@ struct PrefillCfg {
     static constexpr uint32_t kTmemS = 0;                        // S_i at kTmemS + i*128
     static constexpr uint32_t kTmemO = 256;                      // O_i at kTmemO + i*DPAD
     static constexpr float kRescaleThreshold = 8.0f;             // log2 domain
-    static constexpr uint32_t kPolyMask = MFA_POLY_MASK;         // column pairs (c & 3) whose exp2 runs on the FMA pipe
 };
 
 // smem descriptors -------------------------------------------------------------------------------
@@ -150,32 +126,6 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep) 
 __device__ __forceinline__ uint32_t opaque(uint32_t x) {
     asm volatile("" : "+r"(x));
     return x;
-}
-
-// 2^x for two packed floats, x <= ~8, on the FMA pipe: clamp, round-to-nearest split x = n + f (|f| <= 0.5) with
-// the 1.5*2^23 magic constant, 2^f by a degree-3 polynomial with p(0) == 1 exactly (max rel. error 1.0e-4, below
-// the half-ulp of the fp16/bf16 P it is rounded to), exponent added with one integer shift-add.
-// x <= -127 gives exactly +0 (masked columns hold -inf).
-__device__ __forceinline__ uint64_t exp2_poly2(uint64_t x2) {
-    float x0, x1;
-    f2_unpack(x2, x0, x1);
-    x0 = fmaxf(x0, -127.f);
-    x1 = fmaxf(x1, -127.f);
-    const uint64_t xc = f2_pack(x0, x1);
-    const uint64_t magic = f2_pack(12582912.f, 12582912.f);
-    const uint64_t nmagic = f2_pack(-12582912.f, -12582912.f);
-    const uint64_t t = f2_add(xc, magic);
-    const uint64_t n = f2_add(t, nmagic);
-    const uint64_t f = f2_fma(n, f2_pack(-1.f, -1.f), xc);
-    uint64_t q = f2_fma(f, f2_pack(0.05500871315598488f, 0.05500871315598488f), f2_pack(0.24221068620681763f, 0.24221068620681763f));
-    q = f2_fma(q, f, f2_pack(0.6932829022407532f, 0.6932829022407532f));
-    q = f2_fma(q, f, f2_pack(1.f, 1.f));
-    float t0, t1, q0, q1;
-    f2_unpack(t, t0, t1);
-    f2_unpack(q, q0, q1);
-    const float r0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
-    const float r1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
-    return f2_pack(r0, r1);
 }
 
 // One work item = (m-block of kNQ*128 query rows, head, sequence).
@@ -246,7 +196,7 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
 // tiles are still in the softmax, and the epilogue of item n overlaps the first S MMAs of item n+1.  (Measured before:
 // ~7 k cycles from CTA start to the first S and ~3 k of epilogue per ~115 k-cycle item at S=4096, 22 % at S=1024.)
 // All mbarrier parities therefore come from RUNNING counters: items done (q_full / q_empty) and tiles done per Q tile.
-template <typename T, int DPAD, bool kPoly>
+template <typename T, int DPAD>
 __global__ void __launch_bounds__(kPrefillThreads, 1)
     prefill_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const __grid_constant__ PrefillKParams p) {
@@ -284,8 +234,8 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
         for (int i = 0; i < 2; ++i) {
             mbar_init(&q_full[i], 1);
             mbar_init(&s_full[i], 1);
-            mbar_init(&p_lo[i], MFA_PARRIVE_WARP ? 4 : 128);
-            mbar_init(&p_hi[i], MFA_PARRIVE_WARP ? 4 : 128);
+            mbar_init(&p_lo[i], 128);
+            mbar_init(&p_hi[i], 128);
             mbar_init(&o_full[i], 1);
             mbar_init(&q_empty[i], 1);
         }
@@ -323,30 +273,55 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             prefetch_tensormap(&tmK);
             prefetch_tensormap(&tmV);
         }
-        if constexpr (Cfg::kFlat) {
-            uint32_t tail_phase = 0;
-            uint32_t ds = 0;             // double-slot counter, runs across items
-            bool open = false;           // double slot `ds` holds a V tile (half A) and waits for the K tile that closes it
-            uint32_t q_ld[2] = {0, 0};   // loads of Q tile i so far (parity base of q_full / q_empty)
-            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-                const PrefillItem w = prefill_item<kNQ>(p, item);
-                if (!w.valid || w.n_max == 0) continue;   // nothing to load: the softmax warps write the zero rows alone
-                const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
-                const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
-                // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
-                // batches TMA's out-of-bounds fill does it; for packed / paged K/V the producer warp zeroes them.
-                const bool need_tail_fix = (bt != nullptr) || packed_k;
-                // one K or V tile of KV tile j into `dst`; its bytes are counted on `bar` (with the phase's one arrival
-                // when `arrive`, as a bare expect_tx otherwise)
-                auto load_tile = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* bar, bool arrive, int j) {
-                    const int row0 = j * kBN;
+        uint32_t tail_phase = 0;
+        int it = 0;                  // K/V ring position, runs across items
+        uint32_t q_ld[2] = {0, 0};   // loads of Q tile i so far (parity base of q_full / q_empty)
+        for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+            const PrefillItem w = prefill_item<kNQ>(p, item);
+            if (!w.valid) continue;
+            const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
+            const int q_b_coord = p.cu_seqlens_q ? 0 : w.b;
+            // Q tiles of this item -- only the tiles that have KV work (n_i > 0).  A tile without work is never read by
+            // an MMA, so loading it would leave a bulk copy in flight that nobody awaits (it could land after the CTA
+            // exited, or be re-armed before it landed).  q_full / q_empty phases therefore count LOADS of tile i
+            // (q_ld[i]), not items: every load is awaited by the MMA warp before it commits q_empty, and the producer
+            // observes that commit before the next load, so neither barrier ever runs more than one phase ahead.
+#pragma unroll
+            for (int i = 0; i < kNQ; ++i) {
+                if (w.n_i[i] == 0) continue;
+                if (q_ld[i] > 0) mbar_wait(&q_empty[i], (q_ld[i] - 1) & 1);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
+#pragma unroll
+                    for (int sb = 0; sb < Cfg::kSub; ++sb)
+                        tma_load_4d(q_smem + i * Cfg::kQTileBytes + sb * Cfg::kSubBytes, &tmQ, &q_full[i], sb * 64,
+                                    q_row_coord + i * kBM, w.h, q_b_coord);
+                }
+                __syncwarp();
+                ++q_ld[i];
+            }
+            const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
+            const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
+            // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
+            // batches TMA's out-of-bounds fill does it; for packed / paged K/V the producer warp zeroes them.
+            const bool need_tail_fix = (bt != nullptr) || packed_k;
+            for (int j = w.j_lo; j < w.n_max; ++j) {
+                const int row0 = j * kBN;
+                const int rows_valid = min(w.len_k - row0, kBN);
+#pragma unroll 1
+                for (int kv = 0; kv < 2; ++kv, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1;
+                    const CUtensorMap* tm = kv ? &tmV : &tmK;
+                    uint8_t* dst = ring + s * Cfg::kKVTileBytes;
+                    const bool fix = kv && need_tail_fix && rows_valid < kBN;
+                    uint64_t* bar = fix ? tail_bar : &kv_full[s];
+                    mbar_wait(&kv_empty[s], ph ^ 1);
                     if (elect_one()) {
                         if (bt) {
-                            const int rows_valid = min(w.len_k - row0, kBN);
                             const int nchunks = (rows_valid + p.kv_box_rows - 1) / p.kv_box_rows;
                             const int chunk_bytes = p.kv_box_rows * 128;
-                            const uint32_t bytes = (uint32_t)(nchunks * chunk_bytes * Cfg::kSub);
-                            if (arrive) mbar_arrive_expect_tx(bar, bytes); else mbar_expect_tx(bar, bytes);
+                            mbar_arrive_expect_tx(bar, (uint32_t)(nchunks * chunk_bytes * Cfg::kSub));
                             for (int c = 0; c < nchunks; ++c) {
                                 const int row = row0 + c * p.kv_box_rows;
                                 const int pg = row / p.page;
@@ -354,162 +329,30 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                                 const int blk = bt[pg];
 #pragma unroll
                                 for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                    tma_load_4d(dst + sb * Cfg::kSubBytes + c * chunk_bytes, tm, bar, sb * 64, in_page, w.kh, blk);
+                                    tma_load_4d(dst + sb * Cfg::kSubBytes + c * chunk_bytes, tm, bar, sb * 64, in_page,
+                                                w.kh, blk);
                             }
                         } else {
-                            if (arrive) mbar_arrive_expect_tx(bar, Cfg::kKVTileBytes); else mbar_expect_tx(bar, Cfg::kKVTileBytes);
+                            mbar_arrive_expect_tx(bar, Cfg::kKVTileBytes);
 #pragma unroll
                             for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                tma_load_4d(dst + sb * Cfg::kSubBytes, tm, bar, sb * 64, (packed_k ? w.k_off : 0) + row0, w.kh,
-                                            packed_k ? 0 : w.b);
+                                tma_load_4d(dst + sb * Cfg::kSubBytes, tm, bar, sb * 64, (packed_k ? w.k_off : 0) + row0,
+                                            w.kh, packed_k ? 0 : w.b);
                         }
                     }
                     __syncwarp();
-                };
-                const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
-                const int q_b_coord = p.cu_seqlens_q ? 0 : w.b;
-                for (int j = w.j_lo; j < w.n_max; ++j) {
-                    // ---- K_j: half B of the open double slot (closing it), or of a fresh one at the very start
-                    {
-                        const uint32_t st = ds % Cfg::kDS;
-                        if (!open) mbar_wait(&kv_empty[st], ((ds / Cfg::kDS) & 1) ^ 1);
-                        load_tile(&tmK, ring + (2 * st + 1) * Cfg::kKVTileBytes, &kv_full[st], true, j);
-                        ++ds;
-                        open = false;
-                    }
-                    if (j == w.j_lo) {
-                        // Q tiles of this item, AFTER its first K tile (that one closes the previous item's last double
-                        // slot, which must not wait for the Q buffers).  Only tiles with KV work are loaded: a tile
-                        // without work is never read by an MMA, and a bulk copy nobody awaits could land after the CTA
-                        // exited or be re-armed before it landed.  q_full / q_empty phases count LOADS of tile i; the
-                        // MMA warp commits q_empty[i] right after the tile's last S MMA, about one KV step before the
-                        // item ends, so this wait is normally over when the producer gets here.
+                    if (fix) {
+                        // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
+                        mbar_wait(tail_bar, tail_phase);
+                        tail_phase ^= 1;
+                        for (int r = rows_valid; r < kBN; ++r) {
 #pragma unroll
-                        for (int i = 0; i < kNQ; ++i) {
-                            if (w.n_i[i] == 0) continue;
-                            if (q_ld[i] > 0) mbar_wait(&q_empty[i], (q_ld[i] - 1) & 1);
-                            if (elect_one()) {
-                                mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
-#pragma unroll
-                                for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                    tma_load_4d(q_smem + i * Cfg::kQTileBytes + sb * Cfg::kSubBytes, &tmQ, &q_full[i], sb * 64,
-                                                q_row_coord + i * kBM, w.h, q_b_coord);
-                            }
-                            __syncwarp();
-                            ++q_ld[i];
+                            for (int sb = 0; sb < Cfg::kSub; ++sb)
+                                *reinterpret_cast<uint32_t*>(dst + sb * Cfg::kSubBytes + r * 128 + lane * 4) = 0u;
                         }
-                    }
-                    // ---- V_j: half A of the next double slot, left open
-                    {
-                        const uint32_t st = ds % Cfg::kDS;
-                        mbar_wait(&kv_empty[st], ((ds / Cfg::kDS) & 1) ^ 1);
-                        uint8_t* dst = ring + (2 * st) * Cfg::kKVTileBytes;
-                        const int rows_valid = min(w.len_k - j * kBN, kBN);
-                        const bool fix = need_tail_fix && rows_valid < kBN;
-                        load_tile(&tmV, dst, fix ? tail_bar : &kv_full[st], fix, j);
-                        if (fix) {
-                            // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
-                            // (the arrival that closes this double slot -- the next K tile or the final arrive -- follows)
-                            mbar_wait(tail_bar, tail_phase);
-                            tail_phase ^= 1;
-                            for (int r = rows_valid; r < kBN; ++r) {
-#pragma unroll
-                                for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                    *reinterpret_cast<uint32_t*>(dst + sb * Cfg::kSubBytes + r * 128 + lane * 4) = 0u;
-                            }
-                            fence_proxy_async_smem();
-                            __syncwarp();
-                        }
-                        open = true;
-                    }
-                }
-            }
-            if (open) {   // the CTA's last V tile: nothing follows, close its double slot
-                if (elect_one()) mbar_arrive(&kv_full[ds % Cfg::kDS]);
-                __syncwarp();
-            }
-        } else {
-            uint32_t tail_phase = 0;
-            int it = 0;                  // K/V ring position, runs across items
-            uint32_t q_ld[2] = {0, 0};   // loads of Q tile i so far (parity base of q_full / q_empty)
-            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-                const PrefillItem w = prefill_item<kNQ>(p, item);
-                if (!w.valid) continue;
-                const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
-                const int q_b_coord = p.cu_seqlens_q ? 0 : w.b;
-                // Q tiles of this item -- only the tiles that have KV work (n_i > 0).  A tile without work is never read by
-                // an MMA, so loading it would leave a bulk copy in flight that nobody awaits (it could land after the CTA
-                // exited, or be re-armed before it landed).  q_full / q_empty phases therefore count LOADS of tile i
-                // (q_ld[i]), not items: every load is awaited by the MMA warp before it commits q_empty, and the producer
-                // observes that commit before the next load, so neither barrier ever runs more than one phase ahead.
-    #pragma unroll
-                for (int i = 0; i < kNQ; ++i) {
-                    if (w.n_i[i] == 0) continue;
-                    if (q_ld[i] > 0) mbar_wait(&q_empty[i], (q_ld[i] - 1) & 1);
-                    if (elect_one()) {
-                        mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
-    #pragma unroll
-                        for (int sb = 0; sb < Cfg::kSub; ++sb)
-                            tma_load_4d(q_smem + i * Cfg::kQTileBytes + sb * Cfg::kSubBytes, &tmQ, &q_full[i], sb * 64,
-                                        q_row_coord + i * kBM, w.h, q_b_coord);
-                    }
-                    __syncwarp();
-                    ++q_ld[i];
-                }
-                const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
-                const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
-                // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
-                // batches TMA's out-of-bounds fill does it; for packed / paged K/V the producer warp zeroes them.
-                const bool need_tail_fix = (bt != nullptr) || packed_k;
-                for (int j = w.j_lo; j < w.n_max; ++j) {
-                    const int row0 = j * kBN;
-                    const int rows_valid = min(w.len_k - row0, kBN);
-    #pragma unroll 1
-                    for (int kv = 0; kv < 2; ++kv, ++it) {
-                        const int s = it % kStages;
-                        const uint32_t ph = (it / kStages) & 1;
-                        const CUtensorMap* tm = kv ? &tmV : &tmK;
-                        uint8_t* dst = ring + s * Cfg::kKVTileBytes;
-                        const bool fix = kv && need_tail_fix && rows_valid < kBN;
-                        uint64_t* bar = fix ? tail_bar : &kv_full[s];
-                        mbar_wait(&kv_empty[s], ph ^ 1);
-                        if (elect_one()) {
-                            if (bt) {
-                                const int nchunks = (rows_valid + p.kv_box_rows - 1) / p.kv_box_rows;
-                                const int chunk_bytes = p.kv_box_rows * 128;
-                                mbar_arrive_expect_tx(bar, (uint32_t)(nchunks * chunk_bytes * Cfg::kSub));
-                                for (int c = 0; c < nchunks; ++c) {
-                                    const int row = row0 + c * p.kv_box_rows;
-                                    const int pg = row / p.page;
-                                    const int in_page = row - pg * p.page;
-                                    const int blk = bt[pg];
-    #pragma unroll
-                                    for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                        tma_load_4d(dst + sb * Cfg::kSubBytes + c * chunk_bytes, tm, bar, sb * 64, in_page,
-                                                    w.kh, blk);
-                                }
-                            } else {
-                                mbar_arrive_expect_tx(bar, Cfg::kKVTileBytes);
-    #pragma unroll
-                                for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                    tma_load_4d(dst + sb * Cfg::kSubBytes, tm, bar, sb * 64, (packed_k ? w.k_off : 0) + row0,
-                                                w.kh, packed_k ? 0 : w.b);
-                            }
-                        }
+                        fence_proxy_async_smem();
                         __syncwarp();
-                        if (fix) {
-                            // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
-                            mbar_wait(tail_bar, tail_phase);
-                            tail_phase ^= 1;
-                            for (int r = rows_valid; r < kBN; ++r) {
-    #pragma unroll
-                                for (int sb = 0; sb < Cfg::kSub; ++sb)
-                                    *reinterpret_cast<uint32_t*>(dst + sb * Cfg::kSubBytes + r * 128 + lane * 4) = 0u;
-                            }
-                            fence_proxy_async_smem();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(&kv_full[s]);
-                        }
+                        if (lane == 0) mbar_arrive(&kv_full[s]);
                     }
                 }
             }
@@ -551,17 +394,6 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 }
                 __syncwarp();
             };
-            auto issue_PV_at = [&](int i, uint32_t va, bool accumulate, int ks0, int ks1, bool commit_o) {
-                if (elect_one()) {
-                    constexpr uint32_t tb = tmem_base;
-#pragma unroll
-                    for (int ks = ks0; ks < ks1; ++ks)
-                        umma_ts(tb + Cfg::kTmemO + i * DPAD, tb + Cfg::kTmemS + i * 128 + ks * 8,
-                                desc_mnmajor(va, ks), idescO, (accumulate || ks > 0) ? 1u : 0u);
-                    if (commit_o) umma_commit(&o_full[i]);
-                }
-                __syncwarp();
-            };
             auto commit = [&](uint64_t* bar) {
                 if (elect_one()) umma_commit(bar);
                 __syncwarp();
@@ -578,213 +410,71 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
             // without an issue token, P.V + S as one 16-MMA batch (one wait per tile), early non-blocking probes
             // (test_wait: ptxas consumes the predicate at once, the latency stays exposed), splitting the softmax of
             // a tile by key columns over both warpgroups.
-            if constexpr (Cfg::kFlat) {
-                // FLAT STREAM.  The CTA's KV steps form one sequence across its work items.  Step (item, j) waits for
-                // ONE double slot [V_j | K_next] -- K_next is K_{j+1} of the item, or the first K tile of the next work
-                // item when j is the item's last -- issues P.V(j) and S(next) for both Q tiles and releases the slot with
-                // ONE commit: 5 barrier waits per step instead of 7, and the first S MMAs of item n+1 are in the queue
-                // before the last P.V of item n has finished (no drain at the item boundary; with the causal mask the
-                // lone last step of Q tile 1 overlaps the next item's first step of Q tile 0).
-                uint32_t ds = 0;              // double-slot counter, runs across items
-                uint32_t q_ld[2] = {0, 0};    // loads of Q tile i so far (the producer loads a tile only when it has KV work)
-                uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
-                // S_i(jn) of item wx from the K tile at `ka`: the tile's first S waits for its Q load, its last S
-                // releases the Q buffer (so the next item's Q is loaded about one KV step before it is needed)
-                auto s_step = [&](const PrefillItem& wx, int i, int jn, uint32_t ka) {
-                    if (wx.active(i, jn)) {
-                        if (jn == wx.lo_i[i]) {
-                            mbar_wait(&q_full[i], q_ld[i] & 1);
-                            tc_fence_after();
-                        }
-                        if (elect_one()) {
-                            const uint32_t qa = opaque(q_addr) + i * Cfg::kQTileBytes;
-                            constexpr uint32_t tb = tmem_base;
-#pragma unroll
-                            for (int ks = 0; ks < DPAD / 16; ++ks)
-                                umma_ss(tb + Cfg::kTmemS + i * 128, desc_kmajor(qa, ks), desc_kmajor(ka, ks), idescS,
-                                        ks > 0 ? 1u : 0u);
-                            umma_commit(&s_full[i]);
-                            if (jn == wx.n_i[i] - 1) umma_commit(&q_empty[i]);
-                        }
-                        __syncwarp();
-                        if (jn == wx.n_i[i] - 1) ++q_ld[i];
-                    }
-                };
-                auto next_work = [&](int item, PrefillItem& wx) -> int {
-                    for (; item < total_items; item += gridDim.x) {
-                        wx = prefill_item<kNQ>(p, item);
-                        if (wx.valid && wx.n_max > 0) return item;
-                    }
-                    return -1;
-                };
-                PrefillItem w;
-                int item = next_work(blockIdx.x, w);
-                if (item >= 0) {
-                    // the CTA's first double slot holds only K_first
-                    mbar_wait(&kv_full[0], 0);
-                    tc_fence_after();
-#pragma unroll
-                    for (int i = 0; i < kNQ; ++i) s_step(w, i, w.j_lo, ring_addr + Cfg::kKVTileBytes);
-                    commit(&kv_empty[0]);
-                    ds = 1;
-                    mbar_wait(&kv_full[1 % Cfg::kDS], (1 / Cfg::kDS) & 1);   // the double slot of the first KV step
-                    tc_fence_after();
-                }
-                while (item >= 0) {
+            int it = 0;                   // K/V ring position, runs across items
+            uint32_t q_ld[2] = {0, 0};    // loads of Q tile i so far (the producer loads a tile only when it has KV work)
+            uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
+            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+                const PrefillItem w = prefill_item<kNQ>(p, item);
+                if (!w.valid) continue;
 #ifdef MFA_TRACE
-                    tr_on = tr_cta && item == (int)blockIdx.x;
+                tr_on = tr_cta && item == (int)blockIdx.x;
 #endif
-                    PrefillItem wn;
-                    int nitem = -1;
-                    bool looked = false;           // wn / nitem are valid
-                    bool early[2] = {false, false};   // the next item's first S of tile i has been issued already
-                    for (int j = w.j_lo; j < w.n_max; ++j) {
-                        const bool last = (j + 1 == w.n_max);
-                        const bool penult = MFA_EARLY_S && (j + 2 == w.n_max);
-                        if ((last || penult) && !looked) {
-                            nitem = next_work(item + (int)gridDim.x, wn);
-                            looked = true;
-                        }
-                        // (this step's double slot was waited for in the MIDDLE of the previous step, right after Q tile 0's
-                        // batch of S MMAs, when ~4 SS instructions are still queued: at the loop boundary the tensor pipe
-                        // has only ~270 cycles of queued work, and a barrier wait there -- ~90 cycles even when the phase
-                        // completed long ago -- plus the commit and the first P wait left it idle for ~300 cycles per step)
-                        const uint32_t st = ds % Cfg::kDS;
-                        ++ds;
-                        const bool more = !last || nitem >= 0;   // another KV step follows (this item's or the next item's)
-                        MFA_TR(2, j, 0);
-                        const uint32_t va = opaque(ring_addr) + (2 * st) * Cfg::kKVTileBytes;
-                        const uint32_t ka = va + Cfg::kKVTileBytes;
+                const int n_max = w.n_max;
 #pragma unroll
-                        for (int i = 0; i < kNQ; ++i) {
-                            if (w.active(i, j)) {
-                                const uint32_t par = (t_cnt[i] + (uint32_t)(j - w.lo_i[i])) & 1u;
-                                // (the first P.V of an item overwrites O_i: safe, because every softmax thread finished
-                                // the previous item's epilogue -- its TMEM reads of O_i included -- before it released this P)
-#if MFA_PSPLIT
-                                mbar_wait(&p_lo[i], par);
-                                tc_fence_after();
-                                MFA_TR(2, j, 1 + 3 * i);
-                                issue_PV_at(i, va, j > w.lo_i[i], 0, kBN / 32, false);
-                                mbar_wait(&p_hi[i], par);
-                                tc_fence_after();
-                                MFA_TR(2, j, 2 + 3 * i);
-                                issue_PV_at(i, va, j > w.lo_i[i], kBN / 32, kBN / 16, true);
-#else
-                                mbar_wait(&p_hi[i], par);
-                                tc_fence_after();
-                                MFA_TR(2, j, 2 + 3 * i);
-                                issue_PV_at(i, va, j > w.lo_i[i], 0, kBN / 16, true);
-#endif
-                            }
-                            if (!last) s_step(w, i, j + 1, ka);
-                            if (i == 0 && more) {
-                                mbar_wait(&kv_full[ds % Cfg::kDS], (ds / Cfg::kDS) & 1);
-                                tc_fence_after();
-                            }
-                            MFA_TR(2, j, 3 + 3 * i);
-                        }
-                        // the item's last step: both P.V first, then the next item's first S (its Q tiles may still be
-                        // in flight; the wait must not hold back this item's P.V)
-                        if (last && nitem >= 0) {
+                for (int i = 0; i < kNQ; ++i)
+                    if (w.n_i[i] > 0) mbar_wait(&q_full[i], q_ld[i] & 1);
+                if (n_max > 0) {
+                    const int sK = it % kStages;
+                    mbar_wait(&kv_full[sK], (it / kStages) & 1);
+                    ++it;
+                    tc_fence_after();
 #pragma unroll
-                            for (int i = 0; i < kNQ; ++i)
-                                if (!early[i]) s_step(wn, i, wn.j_lo, ka);
-                        }
-                        // the step before: a tile that is already done with this item (no S(j+1), e.g. Q tile 0 under the
-                        // causal mask) takes the next item's first S now.  Its K tile is in the NEXT step's double slot,
-                        // which was waited for above; that slot's release (the next step's commit) covers this MMA too.
-                        if (penult && nitem >= 0) {
-                            const uint32_t ka_next = opaque(ring_addr) + (2 * (ds % Cfg::kDS) + 1) * Cfg::kKVTileBytes;
-#pragma unroll
-                            for (int i = 0; i < kNQ; ++i) {
-                                if (j + 1 >= w.n_i[i] && wn.active(i, wn.j_lo)) {
-                                    s_step(wn, i, wn.j_lo, ka_next);
-                                    early[i] = true;
-                                }
-                            }
-                        }
-                        commit(&kv_empty[st]);
-                    }
-#pragma unroll
-                    for (int i = 0; i < kNQ; ++i) t_cnt[i] += (uint32_t)w.count(i);
-                    w = wn;
-                    item = nitem;
-                }
-            } else {
-                int it = 0;                   // K/V ring position, runs across items
-                uint32_t q_ld[2] = {0, 0};    // loads of Q tile i so far (the producer loads a tile only when it has KV work)
-                uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
-                for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-                    const PrefillItem w = prefill_item<kNQ>(p, item);
-                    if (!w.valid) continue;
-    #ifdef MFA_TRACE
-                    tr_on = tr_cta && item == (int)blockIdx.x;
-    #endif
-                    const int n_max = w.n_max;
-    #pragma unroll
                     for (int i = 0; i < kNQ; ++i)
-                        if (w.n_i[i] > 0) mbar_wait(&q_full[i], q_ld[i] & 1);
-                    if (n_max > 0) {
-                        const int sK = it % kStages;
+                        if (w.active(i, w.j_lo)) issue_S(i, sK);
+                    commit(&kv_empty[sK]);
+                }
+                for (int j = w.j_lo; j < n_max; ++j) {
+                    const int sV = it % kStages;
+                    mbar_wait(&kv_full[sV], (it / kStages) & 1);
+                    ++it;
+                    const bool has_next = (j + 1 < n_max);
+                    int sK = 0;
+                    if (has_next) {
+                        sK = it % kStages;
                         mbar_wait(&kv_full[sK], (it / kStages) & 1);
                         ++it;
-                        tc_fence_after();
-    #pragma unroll
-                        for (int i = 0; i < kNQ; ++i)
-                            if (w.active(i, w.j_lo)) issue_S(i, sK);
-                        commit(&kv_empty[sK]);
                     }
-                    for (int j = w.j_lo; j < n_max; ++j) {
-                        const int sV = it % kStages;
-                        mbar_wait(&kv_full[sV], (it / kStages) & 1);
-                        ++it;
-                        const bool has_next = (j + 1 < n_max);
-                        int sK = 0;
-                        if (has_next) {
-                            sK = it % kStages;
-                            mbar_wait(&kv_full[sK], (it / kStages) & 1);
-                            ++it;
-                        }
-                        tc_fence_after();
-                        MFA_TR(2, j, 0);
-    #pragma unroll
-                        for (int i = 0; i < kNQ; ++i) {
-                            if (w.active(i, j)) {
-                                const uint32_t par = (t_cnt[i] + (uint32_t)(j - w.lo_i[i])) & 1u;
-                                // (the first P.V of an item overwrites O_i: safe, because every softmax thread finished the
-                                // previous item's epilogue -- its TMEM reads of O_i included -- before it released this P)
-#if MFA_PSPLIT
-                                mbar_wait(&p_lo[i], par);
-                                tc_fence_after();
-                                MFA_TR(2, j, 1 + 3 * i);
-                                issue_PV(i, sV, j > w.lo_i[i], 0, kBN / 32, false);
-                                mbar_wait(&p_hi[i], par);
-                                tc_fence_after();
-                                MFA_TR(2, j, 2 + 3 * i);
-                                issue_PV(i, sV, j > w.lo_i[i], kBN / 32, kBN / 16, true);
-#else
-                                mbar_wait(&p_hi[i], par);
-                                tc_fence_after();
-                                MFA_TR(2, j, 2 + 3 * i);
-                                issue_PV(i, sV, j > w.lo_i[i], 0, kBN / 16, true);
-#endif
-                            }
-                            if (w.active(i, j + 1)) issue_S(i, sK);
-                            MFA_TR(2, j, 3 + 3 * i);
-                        }
-                        commit(&kv_empty[sV]);
-                        if (has_next) commit(&kv_empty[sK]);
-                    }
-                    // every MMA that reads this item's Q tiles has been issued: release them to the producer
-    #pragma unroll
+                    tc_fence_after();
+                    MFA_TR(2, j, 0);
+#pragma unroll
                     for (int i = 0; i < kNQ; ++i) {
-                        if (w.n_i[i] > 0) {
-                            commit(&q_empty[i]);
-                            ++q_ld[i];
+                        if (w.active(i, j)) {
+                            const uint32_t par = (t_cnt[i] + (uint32_t)(j - w.lo_i[i])) & 1u;
+                            // (the first P.V of an item overwrites O_i: safe, because every softmax thread finished the
+                            // previous item's epilogue -- its TMEM reads of O_i included -- before it released this P)
+                            mbar_wait(&p_lo[i], par);
+                            tc_fence_after();
+                            MFA_TR(2, j, 1 + 3 * i);
+                            issue_PV(i, sV, j > w.lo_i[i], 0, kBN / 32, false);
+                            mbar_wait(&p_hi[i], par);
+                            tc_fence_after();
+                            MFA_TR(2, j, 2 + 3 * i);
+                            issue_PV(i, sV, j > w.lo_i[i], kBN / 32, kBN / 16, true);
                         }
-                        t_cnt[i] += (uint32_t)w.count(i);
+                        if (w.active(i, j + 1)) issue_S(i, sK);
+                        MFA_TR(2, j, 3 + 3 * i);
                     }
+                    commit(&kv_empty[sV]);
+                    if (has_next) commit(&kv_empty[sK]);
+                }
+                // every MMA that reads this item's Q tiles has been issued: release them to the producer
+#pragma unroll
+                for (int i = 0; i < kNQ; ++i) {
+                    if (w.n_i[i] > 0) {
+                        commit(&q_empty[i]);
+                        ++q_ld[i];
+                    }
+                    t_cnt[i] += (uint32_t)w.count(i);
                 }
             }
         }
@@ -818,37 +508,94 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 mbar_wait(&s_full[i], par);
                 tc_fence_after();
                 MFA_TR(i, j, 1);
-                uint32_t su[128];   // this thread's S row (fp32 bit patterns)
-#pragma unroll
-                for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&su[c * 32]));
+                // this thread's S row (fp32 bit patterns), as two halves of 64 columns: the first half is consumed early
+                uint32_t su_lo[64], su_hi[64];
+                tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[0]));
+                tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[32]));
+                tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[0]));
+                tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[32]));
                 tmem_wait_ld();
                 MFA_TR(i, j, 2);
 
                 const int col0 = j * kBN;
                 const bool need_mask = (col0 + kBN > len_k) || (p.has_hi && (col0 + kBN - 1 > m0 + i * kBM + w.shift_hi));
-                if (need_mask) {
-                    const int lim = p.has_hi ? min(len_k, qrow + 1 + w.shift_hi) : len_k;   // cols >= lim are masked
+                const bool need_mask_lo = p.has_lo && col0 < m0 + i * kBM + kBM - 1 + w.shift_lo;   // the tile's last row has the largest bound
+                auto mask64 = [&](uint32_t (&a)[64], int cbase) {   // a = columns col0 + cbase .. + 63 of the row
+                    if (need_mask) {
+                        const int lim = p.has_hi ? min(len_k, qrow + 1 + w.shift_hi) : len_k;   // cols >= lim are masked
 #pragma unroll
-                    for (int c = 0; c < 128; ++c)
-                        if (col0 + c >= lim) su[c] = 0xff800000u;   // -inf
+                        for (int c = 0; c < 64; ++c)
+                            if (col0 + cbase + c >= lim) a[c] = 0xff800000u;   // -inf
+                    }
+                    if (need_mask_lo) {
+                        const int lim_lo = qrow + w.shift_lo;   // cols < lim_lo are masked
+#pragma unroll
+                        for (int c = 0; c < 64; ++c)
+                            if (col0 + cbase + c < lim_lo) a[c] = 0xff800000u;
+                    }
+                };
+                mask64(su_lo, 0);
+                mask64(su_hi, 64);
+                // P = exp2(S*c2 - ms), packed FFMA2 for the scale, MUFU.EX2, packed add for the row sum, pack to 16 bit
+                const uint64_t c2_2 = f2_pack(c2, c2);
+                auto exp64 = [&](const uint32_t (&a)[64], float ms_, uint32_t (&pk)[32], uint64_t (&acc)[2]) {
+                    const uint64_t nms_2 = f2_pack(-ms_, -ms_);
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const uint64_t x2 = f2_fma(f2_pack(__uint_as_float(a[2 * c]), __uint_as_float(a[2 * c + 1])), c2_2, nms_2);
+                        float x0, x1;
+                        f2_unpack(x2, x0, x1);
+                        const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
+                        acc[c & 1] = f2_add(acc[c & 1], f2_pack(p0, p1));
+                        pk[c] = Elem<T>::pack(p0, p1);
+                    }
+                };
+                // max of 64 columns: 4 independent 3-input max chains
+                auto max64 = [&](const uint32_t (&a)[64]) -> float {
+                    float mx[4];
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) mx[q4] = fmaxf(__uint_as_float(a[q4 * 16]), __uint_as_float(a[q4 * 16 + 1]));
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+#pragma unroll
+                        for (int c = 2; c < 16; c += 2)
+                            mx[q4] = fmax3(mx[q4], __uint_as_float(a[q4 * 16 + c]), __uint_as_float(a[q4 * 16 + c + 1]));
+                    }
+                    return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+                };
+                // SPECULATION.  With the lazy rescale the exponent offset of a tile is the STALE running max unless the
+                // tile's own max exceeds it by more than 2^8 -- which, after the first tile of a row, is rare.  So the first
+                // half of P is exponentiated with the stale max right away, with the row max computed in the same basic
+                // block: the ~70 FMNMX of the max (ALU pipe; ~450 cycles between "S in registers" and the first exponential
+                // in the round-1 trace) run in the shadow of the MUFU work instead of in front of it, and the S -> P latency
+                // -- part of the per-tile critical chain S MMA -> softmax -> P.V MMA -> next S MMA -- shrinks by about that
+                // much.  The S values of the first half die as they are consumed (128 + 32 live values would not fit the
+                // register budget); if any row of the warp does have to move its max, they are read from TMEM again (S is
+                // still intact: P has not been written yet) and the half is recomputed with the new offset.  The results are
+                // bit-identical to the non-speculative order either way.
+                uint32_t pk0[32];
+                uint64_t sum_lo[2] = {0ull, 0ull};
+                const bool spec = MFA_SPEC_EXP && (j > j_first);
+                float tmax;
+                if (spec) {
+                    const float ms_s = (m_run == -INFINITY) ? 0.f : m_run * c2;
+                    const uint64_t nms_2 = f2_pack(-ms_s, -ms_s);
+                    float mxa[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const float s0 = __uint_as_float(su_lo[2 * c]), s1 = __uint_as_float(su_lo[2 * c + 1]);
+                        const uint64_t x2 = f2_fma(f2_pack(s0, s1), c2_2, nms_2);
+                        float x0, x1;
+                        f2_unpack(x2, x0, x1);
+                        const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
+                        sum_lo[c & 1] = f2_add(sum_lo[c & 1], f2_pack(p0, p1));
+                        pk0[c] = Elem<T>::pack(p0, p1);
+                        mxa[c & 3] = fmax3(mxa[c & 3], s0, s1);
+                    }
+                    tmax = fmaxf(fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3])), max64(su_hi));
+                } else {
+                    tmax = fmaxf(max64(su_lo), max64(su_hi));
                 }
-                if (p.has_lo && col0 < m0 + i * kBM + kBM - 1 + w.shift_lo) {   // the tile's last row has the largest bound
-                    const int lim_lo = qrow + w.shift_lo;   // cols < lim_lo are masked
-#pragma unroll
-                    for (int c = 0; c < 128; ++c)
-                        if (col0 + c < lim_lo) su[c] = 0xff800000u;
-                }
-                // row max: 8 independent 3-input max chains, then a tree
-                float mx[8];
-#pragma unroll
-                for (int a = 0; a < 8; ++a) mx[a] = fmaxf(__uint_as_float(su[a * 16]), __uint_as_float(su[a * 16 + 1]));
-#pragma unroll
-                for (int a = 0; a < 8; ++a) {
-#pragma unroll
-                    for (int c = 2; c < 16; c += 2)
-                        mx[a] = fmax3(mx[a], __uint_as_float(su[a * 16 + c]), __uint_as_float(su[a * 16 + c + 1]));
-                }
-                const float tmax = fmaxf(fmax3(mx[0], mx[1], mx[2]), fmax3(fmax3(mx[3], mx[4], mx[5]), mx[6], mx[7]));
                 const float m_new = fmaxf(m_run, tmax);
                 // lazy rescale: keep the stale max unless it grew by more than 2^8
                 const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
@@ -856,8 +603,9 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 const float factor = grow ? ((m_run == -INFINITY) ? 0.f : exp2f((m_run - m_new) * c2)) : 1.f;
                 const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
                 m_run = m_use;
+                const bool any_grow = __any_sync(0xffffffffu, grow);
 
-                if (j > j_first && __any_sync(0xffffffffu, grow)) {
+                if (j > j_first && any_grow) {
                     // O_i currently holds sum_{t<j} P_t V_t: wait for PV(j-1), then rescale our row in place.
                     // Must happen before any part of P(j) is released to the MMA warp.
                     mbar_wait(&o_full[i], par ^ 1u);
@@ -872,47 +620,36 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                         tmem_st32(tO + c * 32, o);
                     }
                 }
-
-                // P = exp2(S*c2 - ms): packed FFMA2 for the scale; per pair of columns either two MUFU.EX2 or the
-                // degree-3 Cody-Waite polynomial on the FMA pipe (pairs with (c & 3) in kPolyMask), because at 128x128
-                // tiles the 16 MUFU lanes/clk cost as many cycles as the two MMAs.  Released to the MMA warp in two
-                // halves so that P.V k-steps 0-3 run while the second half is still being exponentiated.
                 MFA_TR(i, j, 3);
-                const uint64_t c2_2 = f2_pack(c2, c2);
-                const uint64_t nms_2 = f2_pack(-ms, -ms);
-                uint64_t sum2[2] = {0ull, 0ull};
-#pragma unroll
-                for (int hf = 0; hf < 2; ++hf) {
-                    uint32_t pk[32];
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const int e = hf * 64 + 2 * c;
-                        uint64_t x2 = f2_fma(f2_pack(__uint_as_float(su[e]), __uint_as_float(su[e + 1])), c2_2, nms_2);
-                        uint64_t p2;
-                        if (kPoly && ((Cfg::kPolyMask >> (c & 3)) & 1)) {
-                            p2 = exp2_poly2(x2);
-                        } else {
-                            float x0, x1;
-                            f2_unpack(x2, x0, x1);
-                            p2 = f2_pack(ex2_fast(x0), ex2_fast(x1));
-                        }
-                        sum2[c & 1] = f2_add(sum2[c & 1], p2);
-                        float p0, p1;
-                        f2_unpack(p2, p0, p1);
-                        pk[c] = Elem<T>::pack(p0, p1);
-                    }
-                    tmem_st32(tS + hf * 32, pk);
-                    if (MFA_PSPLIT || hf == 1) {
-                        tmem_wait_st();
-                        tc_fence_before();
-#if MFA_PARRIVE_WARP
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(hf == 0 ? &p_lo[i] : &p_hi[i]);
-#else
-                        mbar_arrive(hf == 0 ? &p_lo[i] : &p_hi[i]);
-#endif
-                    }
-                    MFA_TR(i, j, 4 + hf);
+                if (spec && any_grow) {
+                    // a max moved: the S values of the first half were consumed, read them again (S is intact until P is
+                    // stored) and recompute the half with the final offset
+                    uint32_t sr[64];
+                    tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&sr[0]));
+                    tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[32]));
+                    tmem_wait_ld();
+                    mask64(sr, 0);
+                    sum_lo[0] = sum_lo[1] = 0ull;
+                    exp64(sr, ms, pk0, sum_lo);
+                } else if (!spec) {        // first tile of the row
+                    exp64(su_lo, ms, pk0, sum_lo);
+                }
+                // P is released to the MMA warp in two halves so that P.V k-steps 0-3 run while the second half is still
+                // being exponentiated
+                tmem_st32(tS, pk0);
+                tmem_wait_st();
+                tc_fence_before();
+                mbar_arrive(&p_lo[i]);
+                MFA_TR(i, j, 4);
+                uint64_t sum2[2] = {sum_lo[0], sum_lo[1]};
+                {
+                    uint32_t pk1[32];
+                    exp64(su_hi, ms, pk1, sum2);
+                    tmem_st32(tS + 32, pk1);
+                    tmem_wait_st();
+                    tc_fence_before();
+                    mbar_arrive(&p_hi[i]);
+                    MFA_TR(i, j, 5);
                 }
                 float sa, sb, sc, sd;
                 f2_unpack(sum2[0], sa, sb);
@@ -980,22 +717,18 @@ template <typename T, int DPAD>
 static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                     const PrefillKParams& p, cudaStream_t stream) {
     using Cfg = PrefillCfg<DPAD>;
-    // exp2 placement.  Default: every exponential on the MUFU.  The kernel can put a quarter of them on the FMA pipe
-    // (degree-3 polynomial, kPoly = true), which is 2 % faster for an ISOLATED launch on a cold, full-clock GPU (S=1024:
-    // 913 vs 894 TFLOP/s with a sync between launches) -- but any sustained stream of launches sits at the board power
-    // cap (sw_power_cap, 1.6-1.7 GHz), where the extra FMA work costs more clock than the relieved MUFU gives back:
-    // back-to-back loops of >= 200 ms measure MUFU-only +1.5-2 % non-causal and +4-6 % causal at S=1024 and S=2048,
-    // +1.7 % at the headline S=4096 (scripts/prefill_poly_ab.py, bench.py A/B on the same box).  Steady state is what a
-    // serving loop sees, so MUFU-only is the default; MFA_PREFILL_POLY=1 selects the polynomial form.
-    static const bool poly = [] { const char* e = getenv("MFA_PREFILL_POLY"); return e && e[0] == '1'; }();
-    auto kern = poly ? prefill_fwd_kernel<T, DPAD, true> : prefill_fwd_kernel<T, DPAD, false>;
-    static bool attr_done[64][2] = {};
+    // exp2 placement: every exponential on the MUFU.  (Round 1 carried a variant that put a quarter of them on the FMA
+    // pipe as a degree-3 polynomial; it lost 2-4 % in every back-to-back measurement -- the board sits at its power cap
+    // and the extra FMA work costs more clock than the relieved MUFU returns -- and was removed.  The packed
+    // ex2.approx.f16x2 / bf16x2 forms are no way out either: ptxas splits them into two MUFU.EX2 per pair.)
+    auto kern = prefill_fwd_kernel<T, DPAD>;
+    static bool attr_done[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 64 && !attr_done[dev][poly]) {
+    if (dev < 64 && !attr_done[dev]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
         if (e != cudaSuccess) return e;
-        attr_done[dev][poly] = true;
+        attr_done[dev] = true;
     }
     // Fixed-length batches run PERSISTENT: one CTA per SM walks the work items (m-block fastest, so that the CTAs
     // running at the same time share K/V in L2).  With the causal mask an item's cost grows with its m-block, and a

@@ -78,8 +78,10 @@ def test_prefill_headline_shape(mfa, ref_ext, dt, causal):
     assert_close_16bit(ours, ref, _name(dt))
     rows = torch.tensor([0, 1, 127, 128, 255, 256, 2047, 2048, 4095], device="cuda")
     o32 = _rows_oracle(q, k, v, rows, causal)
-    assert (ours[:, rows].float() - o32).abs().max().item() <= _tol(dt)
-    assert (ref[:, rows].float() - o32).abs().max().item() <= _tol(dt)
+    # (the first causal rows copy V almost verbatim: |o| reaches 4-5 with 50 M normal samples, where ONE bf16 rounding of
+    # the output is already 2^-7 = 0.0078 -- hence the bound + one output ulp, for both implementations)
+    assert_close_16bit(ours[:, rows], o32, _name(dt))
+    assert_close_16bit(ref[:, rows], o32, _name(dt))
 
 
 @pytest.mark.parametrize("S,Hq,Hkv,D", [(2048, 32, 8, 128), (4096, 8, 8, 128), (8192, 8, 2, 64)])
@@ -180,29 +182,46 @@ def test_decode_config4(mfa, ref_ext, Hq, Hkv, KV, dt):
     the reference's own decode tests (tests/test_flash_decoding.py:300,361: cache_seqlens = [seqlen_kv] * batch)."""
     q, kc, vc, bt, g = _decode_case(24, KV, Hq, Hkv, 128, 256, dt, KV + Hq)
     sl = torch.full((24,), KV, dtype=torch.int32, device="cuda")
-    ours = mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt, 0)
-    ref = ref_ext.mini_flash_attention_with_kvcache(q, kc, vc, sl, bt, False, 0)
+    _decode_three_way(mfa, ref_ext, q, kc, vc, sl, bt, 0, dt)
+
+
+_REF_DECODE_ROWS = {"total": 0, "bad": 0}
+
+
+def _decode_three_way(mfa, ref_ext, q, kc, vc, sl, bt, splits, dt):
+    """ours == fp32 oracle (hard), and ours == reference on every (batch, head) row where the REFERENCE itself agrees with
+    the oracle.  On the B200 box the reference's decode kernel returns garbage for a varying subset of rows at these sizes
+    (differences of 1e2 ... 3e4 against the fp32 oracle, fp16 and bf16, one split or several; SURVEY quirk Q8: its epilogue
+    aliases shared memory without a barrier) -- those rows cannot pin anything and are counted, not compared."""
+    from oracle import ref_attention as R
+    ours = mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt, splits)
+    ref = ref_ext.mini_flash_attention_with_kvcache(q, kc, vc, sl, bt, False, splits)
+    o32 = R.kvcache_ref(q, kc, vc, sl, bt)
     assert torch.isfinite(ours).all()
-    assert_close_16bit(ours, ref, _name(dt))
+    assert_close_16bit(ours, o32, _name(dt))
+    ref_err = (ref.float() - o32).abs().amax(dim=-1)            # (B, 1, H)
+    good = ref_err <= 2 * _tol(dt)
+    _REF_DECODE_ROWS["total"] += good.numel()
+    _REF_DECODE_ROWS["bad"] += int((~good).sum())
+    if good.any():
+        assert_close_16bit(ours[good], ref[good], _name(dt))
 
 
 @pytest.mark.parametrize("Hq,Hkv", [(24, 24), (32, 8)], ids=["mha", "gqa"])
 @pytest.mark.parametrize("KV", [512, 2048, 8192])
-def test_decode_config4_ragged_lengths_one_split(mfa, ref_ext, Hq, Hkv, KV):
-    """Ragged lengths 1 ... KV.  With num_splits = 1 only: with several splits and lengths much shorter than the
-    capacity the reference returns garbage (differences of 1e2 ... 1e4 against both our kernel and the fp32 oracle, seen
-    on the box; its own tests never combine ragged lengths with splits), so that combination is checked against the
-    fp32 oracle instead (tests/test_decode_gpu.py)."""
+def test_decode_config4_ragged_lengths(mfa, ref_ext, Hq, Hkv, KV):
+    """Ragged lengths 1 ... KV, one split and the split heuristic."""
     q, kc, vc, bt, g = _decode_case(24, KV, Hq, Hkv, 128, 256, torch.bfloat16, KV + Hq + 1)
     sl = torch.randint(1, KV + 1, (24,), device="cuda", generator=g).int()
     sl[0], sl[1] = KV, 1
-    from oracle import ref_attention as R
-    ours = mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt, 1)
-    ref = ref_ext.mini_flash_attention_with_kvcache(q, kc, vc, sl, bt, False, 1)
-    assert_close_16bit(ours, ref, "bf16")
-    # and with the split heuristic on, ours against the fp32 oracle on the same ragged problem
-    ours_auto = mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt, 0)
-    assert (ours_auto.float() - R.kvcache_ref(q, kc, vc, sl, bt)).abs().max().item() <= TOL["bf16"]
+    _decode_three_way(mfa, ref_ext, q, kc, vc, sl, bt, 1, torch.bfloat16)
+    _decode_three_way(mfa, ref_ext, q, kc, vc, sl, bt, 0, torch.bfloat16)
+
+
+def test_reference_decode_rows_report():
+    """Not a check of our code: prints how many (batch, head) rows of the reference's decode output were unusable above."""
+    t, b = _REF_DECODE_ROWS["total"], _REF_DECODE_ROWS["bad"]
+    print(f"\nreference decode rows compared: {t - b} of {t} ({b} rows of the reference disagreed with the fp32 oracle)")
 
 
 @pytest.mark.parametrize("splits", [1, 2, 4, 8])
@@ -215,6 +234,4 @@ def test_decode_long_cache_explicit_splits(mfa, ref_ext, splits):  # tests/test_
     vc = torch.randn(nb, page, Hkv, D, device="cuda", dtype=torch.float16, generator=g)
     bt = torch.randperm(nb, device="cuda", generator=g).reshape(B, KV // page).int()
     sl = torch.tensor([KV, KV - 777], dtype=torch.int32, device="cuda")
-    ours = mfa.flash_attn_with_kvcache(q, kc, vc, sl, bt, splits)
-    ref = ref_ext.mini_flash_attention_with_kvcache(q, kc, vc, sl, bt, False, splits)
-    assert_close_16bit(ours, ref, "fp16")
+    _decode_three_way(mfa, ref_ext, q, kc, vc, sl, bt, splits, torch.float16)
