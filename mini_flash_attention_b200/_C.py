@@ -199,14 +199,26 @@ def mini_flash_attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max
 _FP8 = getattr(torch, "float8_e4m3fn", None)
 
 
+_scale_cache = {}
+
+
 def _kv_scale(s, kv_heads: int, device):
-    """k_scale / v_scale of an e4m3 cache -> (kv_heads,) fp32 device tensor (None stays None = 1.0)."""
+    """k_scale / v_scale of an e4m3 cache -> (kv_heads,) fp32 device tensor (None stays None = 1.0).  No kernel launch on
+    the per-step path: a Python float maps to a cached device tensor, a (kv_heads,) fp32 tensor is used as it is."""
     if s is None:
         return None
     if not isinstance(s, torch.Tensor):
-        s = torch.full((1,), float(s), dtype=torch.float32, device=device)
+        key = (float(s), kv_heads, device)
+        t = _scale_cache.get(key)
+        if t is None:
+            if len(_scale_cache) >= 64:
+                _scale_cache.clear()
+            t = _scale_cache[key] = torch.full((kv_heads,), float(s), dtype=torch.float32, device=device)
+        return t
     _check(s.is_cuda, "k_scale / v_scale must be on CUDA (or Python floats)")
     _check(s.numel() in (1, kv_heads), "k_scale / v_scale must have 1 or kv_num_heads elements")
+    if s.dtype == torch.float32 and s.numel() == kv_heads and s.is_contiguous():
+        return s.reshape(-1)
     return s.to(torch.float32).reshape(-1).expand(kv_heads).contiguous()
 
 

@@ -44,10 +44,9 @@
 #ifndef MFA_REG_HELPER
 #define MFA_REG_HELPER 72
 #endif
-// MFA_SPEC_EXP 1: the first half of P is exponentiated with the stale running max while the row max is still being
-// computed (see the softmax warps); 0: max first, then the exponentials (round-1 order; tuning aid).
-#ifndef MFA_SPEC_EXP
-#define MFA_SPEC_EXP 1
+// MFA_MAX2 1: row max with 2-input FMNMX only (tuning aid: the 3-input form measured ~8 cycles per warp instruction).
+#ifndef MFA_MAX2
+#define MFA_MAX2 0
 #endif
 
 
@@ -144,9 +143,21 @@ struct PrefillItem {
 template <int kNQ>
 __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int item) {
     PrefillItem w;
-    const int mraw = item % p.num_m_blocks;
-    const int rest = item / p.num_m_blocks;
-    const int mblk = (p.has_hi && !p.has_lo) ? (p.num_m_blocks - 1 - mraw) : mraw;   // causal: heaviest (largest m) blocks first
+    int mraw, rest, mblk;
+    if (p.cu_seqlens_q) {
+        // Packed (ragged) batches launch one CTA per item and the hardware hands them out in blockIdx order: the m-block
+        // index is the SLOWEST digit and runs downwards, so the items that exist only in the long sequences -- under the
+        // causal mask also the heaviest ones -- start first and the short tail items fill the gaps at the end
+        // (longest-processing-time order without knowing the lengths on the host).
+        const int per_m = p.heads * p.batch;
+        mraw = item / per_m;
+        rest = item - mraw * per_m;
+        mblk = p.num_m_blocks - 1 - mraw;
+    } else {
+        mraw = item % p.num_m_blocks;
+        rest = item / p.num_m_blocks;
+        mblk = (p.has_hi && !p.has_lo) ? (p.num_m_blocks - 1 - mraw) : mraw;   // causal: heaviest (largest m) blocks first
+    }
     w.h = rest % p.heads;
     w.b = rest / p.heads;
     w.kh = w.h / p.group;
@@ -550,8 +561,19 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                         pk[c] = Elem<T>::pack(p0, p1);
                     }
                 };
-                // max of 64 columns: 4 independent 3-input max chains
+                // max of 64 columns: 4 independent max chains (3-input FMNMX3, or 8 chains of 2-input FMNMX)
                 auto max64 = [&](const uint32_t (&a)[64]) -> float {
+#if MFA_MAX2
+                    float mx[8];
+#pragma unroll
+                    for (int q8 = 0; q8 < 8; ++q8) mx[q8] = fmaxf(__uint_as_float(a[q8 * 8]), __uint_as_float(a[q8 * 8 + 1]));
+#pragma unroll
+                    for (int c = 2; c < 8; ++c) {
+#pragma unroll
+                        for (int q8 = 0; q8 < 8; ++q8) mx[q8] = fmaxf(mx[q8], __uint_as_float(a[q8 * 8 + c]));
+                    }
+                    return fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])), fmaxf(fmaxf(mx[4], mx[5]), fmaxf(mx[6], mx[7])));
+#else
                     float mx[4];
 #pragma unroll
                     for (int q4 = 0; q4 < 4; ++q4) mx[q4] = fmaxf(__uint_as_float(a[q4 * 16]), __uint_as_float(a[q4 * 16 + 1]));
@@ -562,40 +584,10 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                             mx[q4] = fmax3(mx[q4], __uint_as_float(a[q4 * 16 + c]), __uint_as_float(a[q4 * 16 + c + 1]));
                     }
                     return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+#endif
                 };
-                // SPECULATION.  With the lazy rescale the exponent offset of a tile is the STALE running max unless the
-                // tile's own max exceeds it by more than 2^8 -- which, after the first tile of a row, is rare.  So the first
-                // half of P is exponentiated with the stale max right away, with the row max computed in the same basic
-                // block: the ~70 FMNMX of the max (ALU pipe; ~450 cycles between "S in registers" and the first exponential
-                // in the round-1 trace) run in the shadow of the MUFU work instead of in front of it, and the S -> P latency
-                // -- part of the per-tile critical chain S MMA -> softmax -> P.V MMA -> next S MMA -- shrinks by about that
-                // much.  The S values of the first half die as they are consumed (128 + 32 live values would not fit the
-                // register budget); if any row of the warp does have to move its max, they are read from TMEM again (S is
-                // still intact: P has not been written yet) and the half is recomputed with the new offset.  The results are
-                // bit-identical to the non-speculative order either way.
-                uint32_t pk0[32];
-                uint64_t sum_lo[2] = {0ull, 0ull};
-                const bool spec = MFA_SPEC_EXP && (j > j_first);
-                float tmax;
-                if (spec) {
-                    const float ms_s = (m_run == -INFINITY) ? 0.f : m_run * c2;
-                    const uint64_t nms_2 = f2_pack(-ms_s, -ms_s);
-                    float mxa[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const float s0 = __uint_as_float(su_lo[2 * c]), s1 = __uint_as_float(su_lo[2 * c + 1]);
-                        const uint64_t x2 = f2_fma(f2_pack(s0, s1), c2_2, nms_2);
-                        float x0, x1;
-                        f2_unpack(x2, x0, x1);
-                        const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
-                        sum_lo[c & 1] = f2_add(sum_lo[c & 1], f2_pack(p0, p1));
-                        pk0[c] = Elem<T>::pack(p0, p1);
-                        mxa[c & 3] = fmax3(mxa[c & 3], s0, s1);
-                    }
-                    tmax = fmaxf(fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3])), max64(su_hi));
-                } else {
-                    tmax = fmaxf(max64(su_lo), max64(su_hi));
-                }
+                const float tmax = fmaxf(max64(su_lo), max64(su_hi));
+                MFA_TR(i, j, 6);
                 const float m_new = fmaxf(m_run, tmax);
                 // lazy rescale: keep the stale max unless it grew by more than 2^8
                 const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
@@ -604,6 +596,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
                 m_run = m_use;
                 const bool any_grow = __any_sync(0xffffffffu, grow);
+                MFA_TR(i, j, 7);
 
                 if (j > j_first && any_grow) {
                     // O_i currently holds sum_{t<j} P_t V_t: wait for PV(j-1), then rescale our row in place.
@@ -621,19 +614,9 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     }
                 }
                 MFA_TR(i, j, 3);
-                if (spec && any_grow) {
-                    // a max moved: the S values of the first half were consumed, read them again (S is intact until P is
-                    // stored) and recompute the half with the final offset
-                    uint32_t sr[64];
-                    tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&sr[0]));
-                    tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[32]));
-                    tmem_wait_ld();
-                    mask64(sr, 0);
-                    sum_lo[0] = sum_lo[1] = 0ull;
-                    exp64(sr, ms, pk0, sum_lo);
-                } else if (!spec) {        // first tile of the row
-                    exp64(su_lo, ms, pk0, sum_lo);
-                }
+                uint32_t pk0[32];
+                uint64_t sum_lo[2] = {0ull, 0ull};
+                exp64(su_lo, ms, pk0, sum_lo);
                 // P is released to the MMA warp in two halves so that P.V k-steps 0-3 run while the second half is still
                 // being exponentiated
                 tmem_st32(tS, pk0);

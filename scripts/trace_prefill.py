@@ -22,12 +22,12 @@ pr = buf.cpu()[3 * 64 * 8:4 * 64 * 8].view(64, 8)
 t = buf.cpu()[:3 * 64 * 8].view(3, 64, 8)
 t0 = int(t[t > 0].min())
 r = lambda x: int(x) - t0 if int(x) > 0 else -1
-print("softmax events: 0 loop top, 1 S ready, 2 S in regs, 3 max/rescale done, 4 P_lo released, 5 P_hi released")
+print("softmax events: 0 loop top, 1 S ready, 2 S in regs, 6 row max done, 7 grow vote done, 3 rescale done, 4 P_lo released, 5 P_hi released")
 print("mma events (single): 0 K/V ready, 1 p_lo0 seen, 2 p_hi0 seen, 3 PV0+S0 issued, 4 p_lo1 seen, 5 p_hi1 seen, 6 PV1+S1 issued")
 print("mma events (pair): 0 K(j+1) ready, 4 S(j+1) issued, 5 V(j) ready, 1 p_lo seen, 2 p_hi seen (PV lo issued), 3 PV hi issued")
 n = min(S // 128, 64)
 for j in list(range(0, 6)) + list(range(n - 3, n)):
-    print(f"j={j:2d} WG0 {[r(x) for x in t[0, j, :6]]}  WG1 {[r(x) for x in t[1, j, :6]]}  MMA {[r(x) for x in t[2, j, :8]]}  top/Vready {[r(x) for x in pr[j, :2]]}")
+    print(f"j={j:2d} WG0 {[r(x) for x in t[0, j, :8]]}  WG1 {[r(x) for x in t[1, j, :8]]}  MMA {[r(x) for x in t[2, j, :8]]}")
 import statistics
 for role, ev in ((0, 1), (1, 1), (2, 0)):
     d = [int(t[role, j + 1, ev] - t[role, j, ev]) for j in range(4, n - 2)]
@@ -35,9 +35,10 @@ for role, ev in ((0, 1), (1, 1), (2, 0)):
 for role in (0, 1):
     busy = [int(t[role, j, 5] - t[role, j, 1]) for j in range(4, n - 1)]
     wait = [int(t[role, j + 1, 1] - t[role, j, 5]) for j in range(4, n - 2)]
-    seg = [[int(t[role, j, e + 1] - t[role, j, e]) for j in range(4, n - 1)] for e in range(1, 5)]
+    order = [1, 2, 6, 7, 3, 4, 5]
+    seg = [[int(t[role, j, order[e + 1]] - t[role, j, order[e]]) for j in range(4, n - 1)] for e in range(len(order) - 1)]
     print("WG", role, "busy median", statistics.median(busy), "wait-for-S median", statistics.median(wait),
-          "segments ld/max/half0/half1", [statistics.median(s) for s in seg])
+          "segments ld / max / vote / rescale / half0 / half1", [statistics.median(s) for s in seg])
 
 if int(pr[:, 0].max()) > 0:
     print("producer (pair kernel): load index, what, t(before empty-wait), t(issued)")

@@ -200,11 +200,11 @@ def _decode_three_way(mfa, ref_ext, q, kc, vc, sl, bt, splits, dt):
     assert torch.isfinite(ours).all()
     assert_close_16bit(ours, o32, _name(dt))
     ref_err = (ref.float() - o32).abs().amax(dim=-1)            # (B, 1, H)
-    good = ref_err <= 2 * _tol(dt)
+    good = ref_err <= _tol(dt)
     _REF_DECODE_ROWS["total"] += good.numel()
     _REF_DECODE_ROWS["bad"] += int((~good).sum())
-    if good.any():
-        assert_close_16bit(ours[good], ref[good], _name(dt))
+    if good.any():   # both within the bound of the oracle on these rows => within twice the bound of each other
+        assert_close_16bit(ours[good], ref[good], _name(dt), tol_scale=2.0)
 
 
 @pytest.mark.parametrize("Hq,Hkv", [(24, 24), (32, 8)], ids=["mha", "gqa"])
