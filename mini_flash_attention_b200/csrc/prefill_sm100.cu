@@ -44,9 +44,10 @@
 #ifndef MFA_REG_HELPER
 #define MFA_REG_HELPER 72
 #endif
-// MFA_MAX2 1: row max with 2-input FMNMX only (tuning aid: the 3-input form measured ~8 cycles per warp instruction).
-#ifndef MFA_MAX2
-#define MFA_MAX2 0
+// MFA_PACK_PRMT 1: bf16 P is packed on the ALU pipe (integer round-half-up + byte permute) instead of F2FP (tuning aid
+// for the question whether F2FP shares the MUFU's quarter-rate pipe, scripts/pipe_rates.cu).
+#ifndef MFA_PACK_PRMT
+#define MFA_PACK_PRMT 0
 #endif
 
 
@@ -72,6 +73,7 @@ struct Elem<__half> {
         __half2 h = __floats2half2_rn(lo, hi);
         return *reinterpret_cast<uint32_t*>(&h);
     }
+    static __device__ __forceinline__ uint32_t pack_p(float lo, float hi) { return pack(lo, hi); }
 };
 template <>
 struct Elem<__nv_bfloat16> {
@@ -79,6 +81,15 @@ struct Elem<__nv_bfloat16> {
     static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
         __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
         return *reinterpret_cast<uint32_t*>(&h);
+    }
+    // the probabilities P (finite, >= 0): bf16 is the top half of the fp32 pattern, so round-half-up is an integer add
+    // and the pack a byte permute -- ALU-pipe work instead of one F2FP per pair
+    static __device__ __forceinline__ uint32_t pack_p(float lo, float hi) {
+#if MFA_PACK_PRMT
+        return __byte_perm(__float_as_uint(lo) + 0x8000u, __float_as_uint(hi) + 0x8000u, 0x7632);
+#else
+        return pack(lo, hi);
+#endif
     }
 };
 
@@ -558,22 +569,12 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                         f2_unpack(x2, x0, x1);
                         const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
                         acc[c & 1] = f2_add(acc[c & 1], f2_pack(p0, p1));
-                        pk[c] = Elem<T>::pack(p0, p1);
+                        pk[c] = Elem<T>::pack_p(p0, p1);
                     }
                 };
-                // max of 64 columns: 4 independent max chains (3-input FMNMX3, or 8 chains of 2-input FMNMX)
+                // max of 64 columns: 4 independent 3-input max chains (the compiler fuses 2-input chains into FMNMX3 anyway;
+                // the ~300 cycles of this phase are the TMEM read of the row, 16 KB per warp at 64 B/clk, not the ALU work)
                 auto max64 = [&](const uint32_t (&a)[64]) -> float {
-#if MFA_MAX2
-                    float mx[8];
-#pragma unroll
-                    for (int q8 = 0; q8 < 8; ++q8) mx[q8] = fmaxf(__uint_as_float(a[q8 * 8]), __uint_as_float(a[q8 * 8 + 1]));
-#pragma unroll
-                    for (int c = 2; c < 8; ++c) {
-#pragma unroll
-                        for (int q8 = 0; q8 < 8; ++q8) mx[q8] = fmaxf(mx[q8], __uint_as_float(a[q8 * 8 + c]));
-                    }
-                    return fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])), fmaxf(fmaxf(mx[4], mx[5]), fmaxf(mx[6], mx[7])));
-#else
                     float mx[4];
 #pragma unroll
                     for (int q4 = 0; q4 < 4; ++q4) mx[q4] = fmaxf(__uint_as_float(a[q4 * 16]), __uint_as_float(a[q4 * 16 + 1]));
@@ -584,7 +585,6 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                             mx[q4] = fmax3(mx[q4], __uint_as_float(a[q4 * 16 + c]), __uint_as_float(a[q4 * 16 + c + 1]));
                     }
                     return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-#endif
                 };
                 const float tmax = fmaxf(max64(su_lo), max64(su_hi));
                 MFA_TR(i, j, 6);
