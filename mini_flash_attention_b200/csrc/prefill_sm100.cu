@@ -44,11 +44,6 @@
 #ifndef MFA_REG_HELPER
 #define MFA_REG_HELPER 72
 #endif
-// MFA_PACK_PRMT 1: bf16 P is packed on the ALU pipe (integer round-half-up + byte permute) instead of F2FP (tuning aid
-// for the question whether F2FP shares the MUFU's quarter-rate pipe, scripts/pipe_rates.cu).
-#ifndef MFA_PACK_PRMT
-#define MFA_PACK_PRMT 0
-#endif
 
 
 #ifdef MFA_TRACE
@@ -73,7 +68,6 @@ struct Elem<__half> {
         __half2 h = __floats2half2_rn(lo, hi);
         return *reinterpret_cast<uint32_t*>(&h);
     }
-    static __device__ __forceinline__ uint32_t pack_p(float lo, float hi) { return pack(lo, hi); }
 };
 template <>
 struct Elem<__nv_bfloat16> {
@@ -81,15 +75,6 @@ struct Elem<__nv_bfloat16> {
     static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
         __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
         return *reinterpret_cast<uint32_t*>(&h);
-    }
-    // the probabilities P (finite, >= 0): bf16 is the top half of the fp32 pattern, so round-half-up is an integer add
-    // and the pack a byte permute -- ALU-pipe work instead of one F2FP per pair
-    static __device__ __forceinline__ uint32_t pack_p(float lo, float hi) {
-#if MFA_PACK_PRMT
-        return __byte_perm(__float_as_uint(lo) + 0x8000u, __float_as_uint(hi) + 0x8000u, 0x7632);
-#else
-        return pack(lo, hi);
-#endif
     }
 };
 
@@ -569,7 +554,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                         f2_unpack(x2, x0, x1);
                         const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
                         acc[c & 1] = f2_add(acc[c & 1], f2_pack(p0, p1));
-                        pk[c] = Elem<T>::pack_p(p0, p1);
+                        pk[c] = Elem<T>::pack(p0, p1);
                     }
                 };
                 // max of 64 columns: 4 independent 3-input max chains (the compiler fuses 2-input chains into FMNMX3 anyway;

@@ -11,9 +11,12 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import TOL
+from conftest import TOL, assert_close_16bit
 
 pytestmark = pytest.mark.gpu
+
+# the whole matrix runs in both 16-bit types (bf16 is the headline dtype of BASELINE.json; round 1 ran it in fp16 only)
+DTYPES = pytest.mark.parametrize("dt", [torch.float16, torch.bfloat16], ids=["fp16", "bf16"])
 
 
 @pytest.fixture(scope="module")
@@ -40,16 +43,21 @@ def _check(mfa, q, k, v, causal, tol=None):
     assert out.shape == q.shape and out.dtype == q.dtype and out.device == q.device
     assert torch.isfinite(out).all()
     ref = R.attention_ref(q, k, v, causal)
-    err = (out.float() - ref).abs().max().item()
-    tol = tol if tol is not None else (TOL["bf16"] if q.dtype == torch.bfloat16 else TOL["fp16"])
-    assert err <= tol, f"max-abs error {err} > {tol}"
+    if tol is None:
+        # north_star bound + one unit in the last place of the OUTPUT (rows that see one or two keys copy V almost
+        # verbatim: for |o| in [2, 4) a single bf16 rounding of the result is already 2^-7)
+        assert_close_16bit(out, ref, "bf16" if q.dtype == torch.bfloat16 else "fp16")
+    else:
+        err = (out.float() - ref).abs().max().item()
+        assert err <= tol, f"max-abs error {err} > {tol}"
     return out
 
 
 @pytest.mark.parametrize("B,S,H,D", [(2, 512, 8, 64), (1, 256, 4, 64), (1, 4096, 8, 128), (2, 1024, 12, 64),
                                      (1, 1, 8, 64), (32, 128, 8, 64)])
-def test_mha_shapes(mfa, B, S, H, D):  # test_mha.py:22-298
-    _check(mfa, *_qkv(B, S, S, H, H, D), False)
+@DTYPES
+def test_mha_shapes(mfa, B, S, H, D, dt):  # test_mha.py:22-298
+    _check(mfa, *_qkv(B, S, S, H, H, D, dtype=dt), False)
 
 
 def test_mha_normalised_inputs(mfa):  # test_mha.py:55
@@ -58,42 +66,49 @@ def test_mha_normalised_inputs(mfa):  # test_mha.py:55
 
 @pytest.mark.parametrize("D", [32, 64, 96, 128, 256])
 @pytest.mark.parametrize("causal", [False, True])
-def test_head_dims(mfa, D, causal):  # test_mha.py:157, test_causal.py:159, test_gqa.py:244
-    _check(mfa, *_qkv(1, 256, 256, 4, 4, D), causal)
-    _check(mfa, *_qkv(1, 200, 200, 8, 2, D, seed=3), causal)
+@DTYPES
+def test_head_dims(mfa, D, causal, dt):  # test_mha.py:157, test_causal.py:159, test_gqa.py:244
+    _check(mfa, *_qkv(1, 256, 256, 4, 4, D, dtype=dt), causal)
+    _check(mfa, *_qkv(1, 200, 200, 8, 2, D, seed=3, dtype=dt), causal)
 
 
 @pytest.mark.parametrize("D", [160, 192, 224, 8, 72])
-def test_other_head_dims(mfa, D):  # the reference is wrong for 96/160/224; we must simply be correct
-    _check(mfa, *_qkv(1, 130, 130, 2, 2, D), True)
+@DTYPES
+def test_other_head_dims(mfa, D, dt):  # the reference is wrong for 96/160/224; we must simply be correct
+    _check(mfa, *_qkv(1, 130, 130, 2, 2, D, dtype=dt), True)
 
 
 @pytest.mark.parametrize("B", [1, 2, 4, 8])
-def test_batch_sizes(mfa, B):  # test_mha.py:109
-    _check(mfa, *_qkv(B, 256, 256, 4, 4, 64), False)
+@DTYPES
+def test_batch_sizes(mfa, B, dt):  # test_mha.py:109
+    _check(mfa, *_qkv(B, 256, 256, 4, 4, 64, dtype=dt), False)
 
 
 @pytest.mark.parametrize("S", [64, 128, 256, 512, 1024, 2048])
 @pytest.mark.parametrize("causal", [False, True])
-def test_seq_lengths(mfa, S, causal):  # test_mha.py:125, test_causal.py:119
-    _check(mfa, *_qkv(1, S, S, 4, 4, 64), causal)
+@DTYPES
+def test_seq_lengths(mfa, S, causal, dt):  # test_mha.py:125, test_causal.py:119
+    _check(mfa, *_qkv(1, S, S, 4, 4, 64, dtype=dt), causal)
 
 
 @pytest.mark.parametrize("H", [1, 2, 4, 8, 16])
-def test_head_counts(mfa, H):  # test_mha.py:141, test_causal.py:145
-    _check(mfa, *_qkv(1, 256, 256, H, H, 64), True)
+@DTYPES
+def test_head_counts(mfa, H, dt):  # test_mha.py:141, test_causal.py:145
+    _check(mfa, *_qkv(1, 256, 256, H, H, 64, dtype=dt), True)
 
 
 @pytest.mark.parametrize("S", [1, 7, 63, 65, 100, 127, 129, 200, 511, 513, 1000, 2047])
 @pytest.mark.parametrize("causal", [False, True])
-def test_arbitrary_seqlen(mfa, S, causal):  # test_arbitrary_seqlen.py:7,72
-    _check(mfa, *_qkv(2, S, S, 8, 8, 64), causal)
+@DTYPES
+def test_arbitrary_seqlen(mfa, S, causal, dt):  # test_arbitrary_seqlen.py:7,72
+    _check(mfa, *_qkv(2, S, S, 8, 8, 64, dtype=dt), causal)
 
 
 @pytest.mark.parametrize("Hq,Hkv", [(8, 1), (8, 2), (8, 4), (16, 2), (16, 4), (32, 8)])
-def test_gqa_ratios(mfa, Hq, Hkv):  # test_gqa.py:58-82,102,139
-    _check(mfa, *_qkv(1, 512, 512, Hq, Hkv, 64), False)
-    _check(mfa, *_qkv(1, 512, 512, Hq, Hkv, 64, seed=1), True)
+@DTYPES
+def test_gqa_ratios(mfa, Hq, Hkv, dt):  # test_gqa.py:58-82,102,139
+    _check(mfa, *_qkv(1, 512, 512, Hq, Hkv, 64, dtype=dt), False)
+    _check(mfa, *_qkv(1, 512, 512, Hq, Hkv, 64, seed=1, dtype=dt), True)
 
 
 def test_gqa_invalid_ratio_raises(mfa):  # test_gqa.py:206-225
@@ -102,9 +117,10 @@ def test_gqa_invalid_ratio_raises(mfa):  # test_gqa.py:206-225
         mfa.flash_attn_func(q, k, v)
 
 
-def test_gqa_large_causal(mfa):  # test_gqa.py:279, test_causal.py:215,251
-    _check(mfa, *_qkv(2, 2048, 2048, 32, 8, 128), True)
-    _check(mfa, *_qkv(1, 4096, 4096, 8, 8, 128), True)
+@DTYPES
+def test_gqa_large_causal(mfa, dt):  # test_gqa.py:279, test_causal.py:215,251
+    _check(mfa, *_qkv(2, 2048, 2048, 32, 8, 128, dtype=dt), True)
+    _check(mfa, *_qkv(1, 4096, 4096, 8, 8, 128, dtype=dt), True)
 
 
 def test_gqa_long(mfa):  # test_gqa.py:331 (S=8192, (8,2), D64, causal)
@@ -118,10 +134,11 @@ def test_bf16(mfa):
 
 @pytest.mark.parametrize("Sq,Sk", [(128, 512), (100, 333), (512, 128), (300, 77), (1, 200)])
 @pytest.mark.parametrize("causal", [False, True])
-def test_cross_lengths_top_left_causal(mfa, Sq, Sk, causal):
+@DTYPES
+def test_cross_lengths_top_left_causal(mfa, Sq, Sk, causal, dt):
     """Sq != Sk: the causal mask is TOP-LEFT aligned like the reference (prefill.cuh:416); the
     reference itself never checks this case numerically and reads out of bounds for Sq > Sk (we clamp)."""
-    _check(mfa, *_qkv(2, Sq, Sk, 4, 2, 64), causal)
+    _check(mfa, *_qkv(2, Sq, Sk, 4, 2, 64, dtype=dt), causal)
 
 
 def test_causal_differs_from_non_causal_and_default(mfa):  # test_causal.py:68,225
@@ -141,8 +158,9 @@ def test_bitwise_determinism(mfa):  # test_mha.py:93, test_causal.py:182, test_g
 
 
 @pytest.mark.parametrize("causal", [False, True])
-def test_batch_invariance(mfa, causal):  # test_mha.py:173, test_causal.py:192: batch vs per-element < 1e-5
-    q, k, v = _qkv(4, 512, 512, 4, 4, 64)
+@DTYPES
+def test_batch_invariance(mfa, causal, dt):  # test_mha.py:173, test_causal.py:192: batch vs per-element < 1e-5
+    q, k, v = _qkv(4, 512, 512, 4, 4, 64, dtype=dt)
     full = mfa.flash_attn_func(q, k, v, causal=causal)
     for b in range(4):
         one = mfa.flash_attn_func(q[b:b + 1], k[b:b + 1], v[b:b + 1], causal=causal)
