@@ -119,6 +119,7 @@ def dist_setup(n_gpus: int):
     torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
+        os.environ.setdefault("NCCL_DEBUG", "WARN")   # (INFO / VERSION print the NCCL banner on stdout, next to the JSON line)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     return rank, world, local
 

@@ -160,6 +160,8 @@ typedef struct mfa_append_params {
     int32_t seqlen_k;           /* capacity in rows of a contiguous cache (paged: max_blocks_per_seq * page) */
     int32_t batch, s_new, kv_heads, head_dim;   /* head_dim multiple of 8; all 16-byte aligned rows */
     int32_t is_bf16;            /* element size only (2 bytes either way) */
+    int32_t num_blocks;         /* paged: pages in the cache tensors; a block_table entry outside [0, num_blocks) is never
+                                 * written through (the row is skipped like a row beyond the capacity).  0 = unchecked. */
 } mfa_append_params_t;
 int mfa_kvcache_append(const mfa_append_params_t* p, void* cuda_stream);
 

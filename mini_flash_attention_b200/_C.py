@@ -360,6 +360,7 @@ def _append_kv(P, keep, q, k_cache, v_cache, cache_seqlens, k_new, v_new):
     A.block_table, A.block_table_batch_stride = P.block_table, P.block_table_batch_stride
     A.max_blocks_per_seq, A.page_block_size, A.seqlen_k = P.max_blocks_per_seq, P.page_block_size, P.seqlen_k
     A.batch, A.s_new, A.kv_heads, A.head_dim, A.is_bf16 = P.batch, k_new.shape[1], P.kv_heads, P.head_dim, P.is_bf16
+    A.num_blocks = P.num_blocks
     with torch.cuda.device(q.device):
         _lib.check(_lib.load().mfa_kvcache_append(ctypes.byref(A), _stream_ptr(q.device)), "mfa_kvcache_append")
     P.seqlens_k = seqlens_new.data_ptr()

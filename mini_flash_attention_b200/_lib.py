@@ -59,7 +59,7 @@ class MfaAppendParams(ctypes.Structure):
         ("block_table_batch_stride", ctypes.c_int32), ("max_blocks_per_seq", ctypes.c_int32),
         ("page_block_size", ctypes.c_int32), ("seqlen_k", ctypes.c_int32),
         ("batch", ctypes.c_int32), ("s_new", ctypes.c_int32), ("kv_heads", ctypes.c_int32), ("head_dim", ctypes.c_int32),
-        ("is_bf16", ctypes.c_int32),
+        ("is_bf16", ctypes.c_int32), ("num_blocks", ctypes.c_int32),
     ]
 
 

@@ -31,6 +31,8 @@ __global__ void __launch_bounds__(256) kvcache_append_kernel(const __grid_consta
         int row;
         if (p.block_table) {
             const int blk = p.block_table[(long long)b * p.block_table_batch_stride + pos / p.page_block_size];
+            // a stale or negative page id must not become an out-of-bounds STORE (the decode's reads are bounds-checked by TMA)
+            if (blk < 0 || (p.num_blocks > 0 && blk >= p.num_blocks)) continue;
             row = pos % p.page_block_size;
             kb = (long long)blk * p.k_batch_stride;
             vb = (long long)blk * p.v_batch_stride;

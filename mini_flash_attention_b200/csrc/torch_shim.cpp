@@ -377,6 +377,7 @@ static std::tuple<at::Tensor, at::Tensor> kvcache_impl(const at::Tensor& q, cons
         A.seqlen_k = c.P.seqlen_k;
         A.batch = c.P.batch; A.s_new = (int32_t)kn.size(1); A.kv_heads = c.P.kv_heads; A.head_dim = c.P.head_dim;
         A.is_bf16 = c.P.is_bf16;
+        A.num_blocks = c.P.num_blocks;
         check_rc(mfa_kvcache_append(&A, stream_of(q)), "mfa_kvcache_append");
         c.P.seqlens_k = seqlens_new.data_ptr<int32_t>();
     }

@@ -135,6 +135,8 @@ def flash_attn_with_kvcache(
             does not implement) (batch_size, seqlen_new, nheads_k, headdim) new keys/values: written IN PLACE into the
             cache at positions cache_seqlens[b] .. + seqlen_new - 1 (through block_table when paged) before the
             attention, which then covers cache_seqlens + seqlen_new keys.  cache_seqlens itself is not modified.
+            Rows that would fall beyond the cache capacity (or onto a block_table entry outside the cache) are NOT
+            written and the attended length is clamped to the capacity: size the cache for the longest sequence.
         window_size: (new -- SURVEY 8f row 3) sliding window (left, right): the query sits at the last position and
             attends to the last ``left + 1`` keys only (right is irrelevant for one query); KV tiles in front of the
             window are not read, so the step costs O(window), not O(cache_seqlens).  -1 = unbounded.

@@ -1,12 +1,13 @@
 #!/usr/bin/env python
 """Turn ncu artefacts from gpurun_out/ into the tracked summaries under profiles/.
 
-    python scripts/ncu_summarize.py <tag>          e.g. r01a
+    python scripts/ncu_summarize.py <tag> [--out DIR] [key ...]        e.g. r02a prefill decode decode_kv512
 
-Reads  gpurun_out/launches_<tag>.csv, gpurun_out/{prefill,decode}_<tag>.ncu-rep (needs `ncu` on PATH, no GPU)
-Writes profiles/launches_<tag>.txt      per-kernel launch counts / times / share of the step
-       profiles/<kernel>_<tag>.txt      key raw metrics + top stalled SASS instructions
-       profiles/ncu_summary.json        {"prefill": {...}, "decode": {...}} incl. dram_bytes_per_launch (bench.py reads it)
+Reads  gpurun_out/launches_<tag>.csv, gpurun_out/<key>_<tag>.ncu-rep (needs `ncu` on PATH, no GPU; default keys
+       prefill decode).  Runs on the GPU box too, so that only the text summaries travel back (--out gpurun_out/profiles).
+Writes <out>/launches_<tag>.txt      per-kernel launch counts / times / share of the step
+       <out>/<key>_<tag>.txt         key raw metrics + top stalled SASS instructions
+       <out>/ncu_summary.json        {key: {...}} incl. dram_bytes_per_launch (bench.py reads prefill / decode)
 """
 import csv
 import io
@@ -72,6 +73,8 @@ def kernel(tag, key):
     if not os.path.exists(rep):
         return None
     raw = ncu_csv(rep, "raw")
+    if len(raw) < 3:
+        return None
     hdr, units, vals = raw[0], raw[1], raw[2]
     m = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
     src = ncu_csv(rep, "source")
@@ -112,12 +115,19 @@ def kernel(tag, key):
 
 
 def main():
-    tag = sys.argv[1]
+    global PR
+    args = sys.argv[1:]
+    tag = args.pop(0)
+    if "--out" in args:
+        i = args.index("--out")
+        PR = os.path.abspath(args[i + 1])
+        del args[i:i + 2]
+    keys = args or ["prefill", "decode"]
     os.makedirs(PR, exist_ok=True)
     launches(tag)
     sp = os.path.join(PR, "ncu_summary.json")
     summ = json.load(open(sp)) if os.path.exists(sp) else {}
-    for key in ("prefill", "decode"):
+    for key in keys:
         r = kernel(tag, key)
         if r:
             summ[key] = r

@@ -45,6 +45,7 @@ int main(void) {
   printf("%zu %zu %zu %zu %zu %zu\n", offsetof(mfa_params_t, local_window), offsetof(mfa_params_t, causal_bottom_right), sizeof(mfa_append_params_t),
          offsetof(mfa_append_params_t, k_cache), offsetof(mfa_append_params_t, seqlens_out),
          offsetof(mfa_append_params_t, is_bf16));
+  printf("%zu\n", offsetof(mfa_append_params_t, num_blocks));
   return 0; }
 '''
     with tempfile.TemporaryDirectory() as d:
@@ -58,7 +59,7 @@ int main(void) {
                     MfaParams.cu_seqlens_q.offset, MfaParams.k_cache_block_stride.offset, MfaParams.partial_out.offset,
                     MfaParams.kv_fp8.offset, MfaParams.k_scale_ptr.offset, MfaParams.v_scale_ptr.offset,
                     MfaParams.local_window.offset, MfaParams.causal_bottom_right.offset, ctypes.sizeof(A), A.k_cache.offset, A.seqlens_out.offset,
-                    A.is_bf16.offset]
+                    A.is_bf16.offset, A.num_blocks.offset]
 
 
 def test_python_surface_matches_reference():
