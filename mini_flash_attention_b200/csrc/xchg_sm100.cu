@@ -56,6 +56,12 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+// polling load: relaxed at system scope (never served from a stale L1 line); the acquire is ONE fence behind the loop
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 // One CTA of 8 warps per row: the local splits are dealt over the warps (merge.cuh); warp 0 then owns the row -- push,
 // flag, wait, cross-rank merge, store.  Lanes own columns lane*4 + 128*i (head_dim <= 256 => at most 2 float4 per lane).
@@ -104,7 +110,7 @@ __global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_
         const uint32_t* f = p.peer_flags[p.rank] + (int64_t)lane * p.max_rows + row;
         const long long t0 = clock64();
         int polls = 0;
-        while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+        while ((int32_t)(ld_relaxed_sys(f) - epoch) < 0) {
             if (++polls > 128) {
                 if (clock64() - t0 > p.timeout_cycles) {
                     atomicExch(p.ctrs, 1u + (uint32_t)lane);   // reported (and cleared) through mfa_xchg_status / _clear_status
@@ -115,7 +121,8 @@ __global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_
             }
         }
     }
-    timed_out = __any_sync(0xffffffffu, timed_out);   // (also the warp barrier behind the acquiring loads of lanes < world)
+    asm volatile("fence.acq_rel.sys;" ::: "memory");   // acquire: the flags were seen, now the rows may be read
+    timed_out = __any_sync(0xffffffffu, timed_out);   // (also the warp barrier behind the acquiring lanes)
 
     // ---- 4. merge the R partial rows (L2 loads: the lines were written by peers, never trust L1)
     const float* base = p.peer_data[p.rank] + ((int64_t)parity * p.world * p.max_rows + row) * DS;
