@@ -38,11 +38,22 @@
 
 // Register split of the 64 K registers of an SM over the CTA's 384 threads (setmaxnreg): 256 softmax threads and
 // 128 data-movement / MMA / allocator threads; 256 * SOFTMAX + 128 * HELPER <= 65536.
+// MFA_ROW_SPLIT 2: TWO softmax threads per query row (each takes 64 of the tile's 128 key columns), i.e. 8 softmax warps
+// per Q tile, two per SM sub-partition.  One warp per sub-partition cannot keep the MUFU busy (scripts/pipe_rates.cu:
+// 9.1 cycles per MUFU.EX2 from one warp, 8.07 from two) and pays the whole 16 KB TMEM read of its row block alone; with
+// two, the TMEM read, the max and the exponentials of a tile all take about half as long, which shortens the per-tile
+// chain S MMA -> softmax -> P.V -> next S MMA that bounds the kernel.  1 = one thread per row (round 1).
+#ifndef MFA_ROW_SPLIT
+#define MFA_ROW_SPLIT 2
+#endif
 #ifndef MFA_REG_SOFTMAX
-#define MFA_REG_SOFTMAX 216
+#define MFA_REG_SOFTMAX 216   // 384-thread CTA (one thread per row, or head_dim 256)
 #endif
 #ifndef MFA_REG_HELPER
 #define MFA_REG_HELPER 72
+#endif
+#ifndef MFA_REG_SOFTMAX_640
+#define MFA_REG_SOFTMAX_640 104   // 640-thread CTA (two threads per row, two Q tiles): 512 * 104 + 128 * 72 <= 65536
 #endif
 
 
@@ -83,6 +94,10 @@ struct PrefillCfg {
     static constexpr int kBM = kPrefillBlockM;
     static constexpr int kBN = kPrefillBlockN;
     static constexpr int kNQ = (DPAD <= 128) ? 2 : 1;            // Q tiles per CTA (TMEM budget)
+    static constexpr int kRS = MFA_ROW_SPLIT;                    // softmax threads per query row
+    static constexpr int kSoftmaxWarps = kNQ * 4 * kRS;
+    static constexpr int kThreads = (kSoftmaxWarps + 4) * 32;    // + one warpgroup {TMA warp, MMA warp, TMEM warp, spare}
+    static constexpr int kXchgBytes = 2 * 2 * 2 * 128 * 4;       // row-max / row-sum exchange between the two threads of a row
     static constexpr int kSub = DPAD / 64;                       // 64-column (128-byte) sub-tiles per row
     static constexpr int kSubBytes = 128 * 128;                  // 128 rows x 128 B
     static constexpr int kQTileBytes = kSub * kSubBytes;
@@ -94,7 +109,7 @@ struct PrefillCfg {
     static constexpr int kQBytes = kNQ * kQTileBytes;
     static constexpr int kRingBytes = kStages * kKVTileBytes;
     static constexpr int kBarOffset = kQBytes + kRingBytes;
-    static constexpr int kSmemBytes = kBarOffset + 512 + 1024;   // barriers + alignment slack
+    static constexpr int kSmemBytes = kBarOffset + 512 + kXchgBytes + 1024;   // barriers + exchange + alignment slack
     static constexpr uint32_t kTmemCols = 512;
     static constexpr uint32_t kTmemS = 0;                        // S_i at kTmemS + i*128
     static constexpr uint32_t kTmemO = 256;                      // O_i at kTmemO + i*DPAD
@@ -204,7 +219,7 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
 // ~7 k cycles from CTA start to the first S and ~3 k of epilogue per ~115 k-cycle item at S=4096, 22 % at S=1024.)
 // All mbarrier parities therefore come from RUNNING counters: items done (q_full / q_empty) and tiles done per Q tile.
 template <typename T, int DPAD>
-__global__ void __launch_bounds__(kPrefillThreads, 1)
+__global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
     prefill_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const __grid_constant__ PrefillKParams p) {
     using Cfg = PrefillCfg<DPAD>;
@@ -231,8 +246,11 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int total_items = p.num_m_blocks * p.heads * p.batch;
+    constexpr int kRS = Cfg::kRS;
+    constexpr int kWarpTma = Cfg::kSoftmaxWarps, kWarpMma = kWarpTma + 1, kWarpTmem = kWarpTma + 2;
+    float* xchg = reinterpret_cast<float*>(smem + Cfg::kBarOffset + 512);   // [2 buffers][2 Q tiles][2 halves][128 rows]
 #ifdef MFA_TRACE
-    const bool tr_cta = p.trace && blockIdx.x == 0 && lane == 0 && (warp == 9 || (warp & 3) == 0);
+    const bool tr_cta = p.trace && blockIdx.x == 0 && lane == 0 && (warp == kWarpMma || ((warp & 3) == 0 && (warp / 4) % kRS == 0));
     bool tr_on = false;
 #endif
 
@@ -253,7 +271,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
         }
         fence_barrier_init();
     }
-    if (warp == 10) {
+    if (warp == kWarpTmem) {
         tmem_alloc(tmem_slot, Cfg::kTmemCols);
         tmem_relinquish();
     }
@@ -269,9 +287,9 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
     // Register re-balancing: the launch gives every thread 168 registers (65536 / 384 threads); the
     // data-movement warpgroup hands most of its share to the two softmax warpgroups (whole S row in registers).
     // (Each setmaxnreg sits at the top of its own role branch so that ptxas sees the budget per region.)
-    if (warp >= 8) {
+    if (warp >= kWarpTma) {
       asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MFA_REG_HELPER));
-    if (warp == 8) {
+    if (warp == kWarpTma) {
         // ======================================================================= TMA producer
         // Warp-uniform control flow with one ELECTED lane issuing (see the MMA warp): under a divergent
         // `if (lane == 0)` ptxas cannot keep the TMA operands in uniform registers.
@@ -364,7 +382,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 }
             }
         }
-    } else if (warp == 9) {
+    } else if (warp == kWarpMma) {
         // ======================================================================= MMA issuer
         // The whole warp runs the (warp-uniform) control flow and the barrier waits; one elected lane issues the
         // tcgen05 instructions.  Written this way -- not `if (lane == 0)` -- so that ptxas keeps descriptors and
@@ -496,16 +514,29 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
         }
     }
     } else {
-      asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MFA_REG_SOFTMAX));
-      if (warp < 4 * kNQ) {
+      asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(Cfg::kThreads == 640 ? MFA_REG_SOFTMAX_640 : MFA_REG_SOFTMAX));
+      if (warp < Cfg::kSoftmaxWarps) {
         // ======================================================================= softmax warpgroups
-        const int i = warp >> 2;
+        // warp -> (Q tile i, column half hf, TMEM lane quarter): a warp may only touch TMEM lanes 32 * (warp % 4) ... + 31,
+        // so the two warps that share the rows of a quarter are warp and warp + 4 -- both on the same SM sub-partition
+        const int i = warp / (4 * kRS);
+        const int hf = (warp >> 2) % kRS;                         // 0: key columns 0-63 of a tile (kRS = 2), 1: 64-127
         const int row_in_tile = (warp & 3) * 32 + lane;
         const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
         const uint32_t tS = tmem_base + lane_sel + Cfg::kTmemS + i * 128;
         const uint32_t tO = tmem_base + lane_sel + Cfg::kTmemO + i * DPAD;
         const float c2 = p.scale_log2;
         uint32_t t_cnt = 0;   // KV tiles this warpgroup has processed so far (parity base)
+        uint32_t x_cnt = 0;   // row exchanges so far (kRS = 2: double-buffer index of the exchange area)
+        // value exchange between the two threads of a row (one barrier per exchange; 2 buffers: a thread can be at most
+        // one exchange ahead of its partner, who has finished reading buffer b before it arrives at the barrier of b ^ 1)
+        auto row_exchange = [&](float mine) -> float {
+            float* buf = xchg + ((x_cnt & 1u) * 2 + i) * 256;
+            buf[hf * 128 + row_in_tile] = mine;
+            named_bar_sync(1 + i, 128 * kRS);
+            ++x_cnt;
+            return buf[(hf ^ 1) * 128 + row_in_tile];
+        };
         for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
             const PrefillItem w = prefill_item<kNQ>(p, item);
             if (!w.valid) continue;
@@ -524,15 +555,6 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                 mbar_wait(&s_full[i], par);
                 tc_fence_after();
                 MFA_TR(i, j, 1);
-                // this thread's S row (fp32 bit patterns), as two halves of 64 columns: the first half is consumed early
-                uint32_t su_lo[64], su_hi[64];
-                tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[0]));
-                tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[32]));
-                tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[0]));
-                tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[32]));
-                tmem_wait_ld();
-                MFA_TR(i, j, 2);
-
                 const int col0 = j * kBN;
                 const bool need_mask = (col0 + kBN > len_k) || (p.has_hi && (col0 + kBN - 1 > m0 + i * kBM + w.shift_hi));
                 const bool need_mask_lo = p.has_lo && col0 < m0 + i * kBM + kBM - 1 + w.shift_lo;   // the tile's last row has the largest bound
@@ -550,8 +572,6 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                             if (col0 + cbase + c < lim_lo) a[c] = 0xff800000u;
                     }
                 };
-                mask64(su_lo, 0);
-                mask64(su_hi, 64);
                 // P = exp2(S*c2 - ms), packed FFMA2 for the scale, MUFU.EX2, packed add for the row sum, pack to 16 bit
                 const uint64_t c2_2 = f2_pack(c2, c2);
                 auto exp64 = [&](const uint32_t (&a)[64], float ms_, uint32_t (&pk)[32], uint64_t (&acc)[2]) {
@@ -567,7 +587,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     }
                 };
                 // max of 64 columns: 4 independent 3-input max chains (the compiler fuses 2-input chains into FMNMX3 anyway;
-                // the ~300 cycles of this phase are the TMEM read of the row, 16 KB per warp at 64 B/clk, not the ALU work)
+                // most of this phase is the TMEM read of the row block, 64 B/clk, not the ALU work)
                 auto max64 = [&](const uint32_t (&a)[64]) -> float {
                     float mx[4];
 #pragma unroll
@@ -580,53 +600,114 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     }
                     return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
                 };
-                const float tmax = fmaxf(max64(su_lo), max64(su_hi));
-                MFA_TR(i, j, 6);
-                const float m_new = fmaxf(m_run, tmax);
-                // lazy rescale: keep the stale max unless it grew by more than 2^8
-                const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
-                const float m_use = grow ? m_new : m_run;
-                const float factor = grow ? ((m_run == -INFINITY) ? 0.f : exp2f((m_run - m_new) * c2)) : 1.f;
-                const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
-                m_run = m_use;
-                const bool any_grow = __any_sync(0xffffffffu, grow);
-                MFA_TR(i, j, 7);
-
-                if (j > j_first && any_grow) {
-                    // O_i currently holds sum_{t<j} P_t V_t: wait for PV(j-1), then rescale our row in place.
-                    // Must happen before any part of P(j) is released to the MMA warp.
+                // lazy rescale of this thread's part of the O row (columns [oc0, oc0 + ocn)) by `factor`: O_i holds
+                // sum_{t<j} P_t V_t; wait for PV(j-1) first.  Must happen before any part of P(j) is released.
+                auto rescale_o = [&](float factor, int oc0, int ocn) {
                     mbar_wait(&o_full[i], par ^ 1u);
                     tc_fence_after();
-#pragma unroll
-                    for (int c = 0; c < DPAD / 32; ++c) {
-                        uint32_t o[32];
-                        tmem_ld32(tO + c * 32, o);
+                    // (16 columns at a time: this rare path runs with the whole S row live in registers)
+#pragma unroll 1
+                    for (int c = oc0; c < oc0 + ocn; c += 16) {
+                        uint32_t o[16];
+                        tmem_ld16(tO + c, o);
                         tmem_wait_ld();
 #pragma unroll
-                        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * factor);
-                        tmem_st32(tO + c * 32, o);
+                        for (int e = 0; e < 16; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * factor);
+                        tmem_st16(tO + c, o);
                     }
-                }
-                MFA_TR(i, j, 3);
-                uint32_t pk0[32];
-                uint64_t sum_lo[2] = {0ull, 0ull};
-                exp64(su_lo, ms, pk0, sum_lo);
-                // P is released to the MMA warp in two halves so that P.V k-steps 0-3 run while the second half is still
-                // being exponentiated
-                tmem_st32(tS, pk0);
-                tmem_wait_st();
-                tc_fence_before();
-                mbar_arrive(&p_lo[i]);
-                MFA_TR(i, j, 4);
-                uint64_t sum2[2] = {sum_lo[0], sum_lo[1]};
-                {
-                    uint32_t pk1[32];
-                    exp64(su_hi, ms, pk1, sum2);
-                    tmem_st32(tS + 32, pk1);
+                };
+                uint64_t sum2[2] = {0ull, 0ull};
+                float factor;
+                if constexpr (kRS == 2) {
+                    // ---- two threads per row: this one owns key columns [64 hf, 64 hf + 64) of the tile
+                    uint32_t su[64];
+                    tmem_ld32(tS + hf * 64, *reinterpret_cast<uint32_t(*)[32]>(&su[0]));
+                    tmem_ld32(tS + hf * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&su[32]));
+                    tmem_wait_ld();
+                    MFA_TR(i, j, 2);
+                    mask64(su, hf * 64);
+                    const float my_max = max64(su);
+                    MFA_TR(i, j, 6);
+                    // The exchange is also the point behind which P may overwrite S: the partner has its S columns in
+                    // registers (P of the second half lands on columns 32-63 of the tile, which belong to the first).
+                    const float tmax = fmaxf(my_max, row_exchange(my_max));
+                    const float m_new = fmaxf(m_run, tmax);
+                    // lazy rescale: keep the stale max unless it grew by more than 2^8 (both threads of a row decide alike)
+                    const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
+                    const float m_use = grow ? m_new : m_run;
+                    factor = grow ? ((m_run == -INFINITY) ? 0.f : exp2f((m_run - m_new) * c2)) : 1.f;
+                    const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
+                    m_run = m_use;
+                    const bool any_grow = __any_sync(0xffffffffu, grow);
+                    MFA_TR(i, j, 7);
+                    if (j > j_first && any_grow) rescale_o(factor, hf * (DPAD / 2), DPAD / 2);
+                    MFA_TR(i, j, 3);
+                    {   // (two stores of 16 packed columns: the S registers die as they are consumed, the budget is 104)
+                        const uint64_t nms_2 = f2_pack(-ms, -ms);
+#pragma unroll
+                        for (int k = 0; k < 2; ++k) {
+                            uint32_t pk[16];
+#pragma unroll
+                            for (int c = 0; c < 16; ++c) {
+                                const int e = 32 * k + 2 * c;
+                                const uint64_t x2 = f2_fma(f2_pack(__uint_as_float(su[e]), __uint_as_float(su[e + 1])), c2_2, nms_2);
+                                float x0, x1;
+                                f2_unpack(x2, x0, x1);
+                                const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
+                                sum2[c & 1] = f2_add(sum2[c & 1], f2_pack(p0, p1));
+                                pk[c] = Elem<T>::pack(p0, p1);
+                            }
+                            tmem_st16(tS + hf * 32 + k * 16, pk);
+                        }
+                    }
                     tmem_wait_st();
                     tc_fence_before();
-                    mbar_arrive(&p_hi[i]);
-                    MFA_TR(i, j, 5);
+                    mbar_arrive(hf == 0 ? &p_lo[i] : &p_hi[i]);   // (each half of P comes from its own 128 threads)
+                    MFA_TR(i, j, 4 + hf);
+                } else {
+                    // ---- one thread per row
+                    uint32_t su_lo[64], su_hi[64];
+                    tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[0]));
+                    tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[32]));
+                    tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[0]));
+                    tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[32]));
+                    tmem_wait_ld();
+                    MFA_TR(i, j, 2);
+                    mask64(su_lo, 0);
+                    mask64(su_hi, 64);
+                    const float tmax = fmaxf(max64(su_lo), max64(su_hi));
+                    MFA_TR(i, j, 6);
+                    const float m_new = fmaxf(m_run, tmax);
+                    // lazy rescale: keep the stale max unless it grew by more than 2^8
+                    const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
+                    const float m_use = grow ? m_new : m_run;
+                    factor = grow ? ((m_run == -INFINITY) ? 0.f : exp2f((m_run - m_new) * c2)) : 1.f;
+                    const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
+                    m_run = m_use;
+                    const bool any_grow = __any_sync(0xffffffffu, grow);
+                    MFA_TR(i, j, 7);
+                    if (j > j_first && any_grow) rescale_o(factor, 0, DPAD);
+                    MFA_TR(i, j, 3);
+                    // P is released to the MMA warp in two halves so that P.V k-steps 0-3 run while the second half is still
+                    // being exponentiated
+                    {
+                        uint32_t pk0[32];
+                        exp64(su_lo, ms, pk0, sum2);
+                        tmem_st32(tS, pk0);
+                        tmem_wait_st();
+                        tc_fence_before();
+                        mbar_arrive(&p_lo[i]);
+                        MFA_TR(i, j, 4);
+                    }
+                    {
+                        uint32_t pk1[32];
+                        exp64(su_hi, ms, pk1, sum2);
+                        tmem_st32(tS + 32, pk1);
+                        tmem_wait_st();
+                        tc_fence_before();
+                        mbar_arrive(&p_hi[i]);
+                        MFA_TR(i, j, 5);
+                    }
                 }
                 float sa, sb, sc, sd;
                 f2_unpack(sum2[0], sa, sb);
@@ -645,12 +726,16 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
                     mbar_wait(&o_full[i], (t_cnt + (uint32_t)n_mine - 1u) & 1u);
                     tc_fence_after();
                 }
-                const float inv = (l_run == 0.f || l_run != l_run) ? 1.f : 1.f / l_run;   // prefill.cuh:604-605
-                if (p.lse != nullptr && row_ok)   // natural-log LSE of the scaled scores (the reference drops it, api.cpp:436)
+                // (two threads per row: each holds the sum over its own key columns)
+                const float l_row = (kRS == 2) ? l_run + row_exchange(l_run) : l_run;
+                const float inv = (l_row == 0.f || l_row != l_row) ? 1.f : 1.f / l_row;   // prefill.cuh:604-605
+                if (p.lse != nullptr && row_ok && hf == 0)   // natural-log LSE of the scaled scores (the reference drops it, api.cpp:436)
                     p.lse[(int64_t)w.b * p.lse_batch_stride + (int64_t)w.h * p.lse_head_stride + w.q_off + qrow] =
-                        (l_run == 0.f || l_run != l_run) ? -INFINITY : (m_run * c2 + log2f(l_run)) * 0.6931471805599453f;
+                        (l_row == 0.f || l_row != l_row) ? -INFINITY : (m_run * c2 + log2f(l_row)) * 0.6931471805599453f;
+                constexpr int kChunks = DPAD / 32 / kRS;   // 32-column chunks of the O row per thread
 #pragma unroll
-                for (int c = 0; c < DPAD / 32; ++c) {
+                for (int c0 = 0; c0 < kChunks; ++c0) {
+                    const int c = hf * kChunks + c0;
                     uint32_t o[32];
                     if (n_mine > 0) {   // warp-uniform
                         tmem_ld32(tO + c * 32, o);
@@ -682,7 +767,7 @@ __global__ void __launch_bounds__(kPrefillThreads, 1)
     // ---- teardown
     tc_fence_before();
     __syncthreads();
-    if (warp == 10) {
+    if (warp == kWarpTmem) {
         tc_fence_after();
         tmem_dealloc(tmem_base, Cfg::kTmemCols);
     }
@@ -728,7 +813,7 @@ static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& t
         }
     }
     dim3 grid((unsigned)ctas, 1, 1);
-    kern<<<grid, kPrefillThreads, Cfg::kSmemBytes, stream>>>(tmQ, tmK, tmV, p);
+    kern<<<grid, Cfg::kThreads, Cfg::kSmemBytes, stream>>>(tmQ, tmK, tmV, p);
     return cudaGetLastError();
 }
 
