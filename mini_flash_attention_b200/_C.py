@@ -367,10 +367,25 @@ def _append_kv(P, keep, q, k_cache, v_cache, cache_seqlens, k_new, v_new):
     return (seqlens_new, kn, vn)
 
 
+def _empty_shard_partial(q, k_cache, block_table):
+    """A KV shard with no rows (a rank beyond the end of a short context): O = 0, LSE = -inf, no kernel launch.  The merge
+    (merge.cuh) gives such a partial weight exp2(-inf) = 0."""
+    if q.numel() == 0 or (block_table is None and k_cache.shape[1] == 0) or k_cache.numel() == 0:
+        batch, _, num_heads, head_dim = q.shape
+        return (torch.zeros(batch, num_heads, head_dim, dtype=torch.float32, device=q.device),
+                torch.full((batch, num_heads), float("-inf"), dtype=torch.float32, device=q.device))
+    return None
+
+
+
+
 def decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits=0):
     """KV-shard building block of the multi-GPU decode: normalised fp32 partial O (B,H,D) and LSE (B,H)
     over this rank's part of the KV axis (LSE = -inf, O = 0 where the shard is empty).  New -- the reference
     has no multi-GPU path; the arithmetic is its split-KV partial (decode.cuh:645-661)."""
+    empty = _empty_shard_partial(q, k_cache, block_table)
+    if empty is not None:
+        return empty
     P, keep = _decode_params(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)
     batch, _, num_heads, head_dim = q.shape
     o = torch.empty(batch, num_heads, head_dim, dtype=torch.float32, device=q.device)
@@ -533,6 +548,9 @@ if _shim is not None:
         return _shim.mini_flash_attention_with_kvcache(q, k_cache, v_cache, cache_seqlens, block_table, causal, num_splits)
 
     def decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits=0):
+        empty = _empty_shard_partial(q, k_cache, block_table)
+        if empty is not None:
+            return empty
         if isinstance(cache_seqlens, int):
             cache_seqlens = torch.full((q.shape[0],), cache_seqlens, dtype=torch.int32, device=q.device)
         return _shim.decode_partial(q, k_cache, v_cache, cache_seqlens, block_table, num_splits)

@@ -30,30 +30,26 @@
 // kv_head = head / group (:49); varlen through cu_seqlens (:19-33); paged K/V through block_table --
 // gathered per page box, not per 64-row tile (fixes quirk Q3 of SURVEY.md).
 #include <cstdlib>
+#include <type_traits>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
 #include "kparams.h"
 #include "ptx.cuh"
 
-// Register split of the 64 K registers of an SM over the CTA's 384 threads (setmaxnreg): 256 softmax threads and
-// 128 data-movement / MMA / allocator threads; 256 * SOFTMAX + 128 * HELPER <= 65536.
-// MFA_ROW_SPLIT 2: TWO softmax threads per query row (each takes 64 of the tile's 128 key columns), i.e. 8 softmax warps
-// per Q tile, two per SM sub-partition.  One warp per sub-partition cannot keep the MUFU busy (scripts/pipe_rates.cu:
-// 9.1 cycles per MUFU.EX2 from one warp, 8.07 from two) and pays the whole 16 KB TMEM read of its row block alone; with
-// two, the TMEM read, the max and the exponentials of a tile all take about half as long, which shortens the per-tile
-// chain S MMA -> softmax -> P.V -> next S MMA that bounds the kernel.  1 = one thread per row (round 1).
-#ifndef MFA_ROW_SPLIT
-#define MFA_ROW_SPLIT 2
+// Register split over the CTA's 384 threads (setmaxnreg): 256 softmax threads and 128 data-movement / MMA / allocator
+// threads.  setmaxnreg only moves registers INSIDE the pool the CTA was launched with -- 168 registers x 384 threads =
+// 64512, not the SM's 65536 -- so 256 * SOFTMAX + 128 * HELPER must be <= 64512 (216 / 72 is exact; a split that needs
+// more blocks in setmaxnreg.inc for ever).
+// Every MFA_POLY_EVERY-th pair of exponentials of an unmasked tile goes to the FMA pipe as a polynomial (0 = none).
+#ifndef MFA_POLY_EVERY
+#define MFA_POLY_EVERY 0
 #endif
 #ifndef MFA_REG_SOFTMAX
-#define MFA_REG_SOFTMAX 216   // 384-thread CTA (one thread per row, or head_dim 256)
+#define MFA_REG_SOFTMAX 216
 #endif
 #ifndef MFA_REG_HELPER
 #define MFA_REG_HELPER 72
-#endif
-#ifndef MFA_REG_SOFTMAX_640
-#define MFA_REG_SOFTMAX_640 104   // 640-thread CTA (two threads per row, two Q tiles): 512 * 104 + 128 * 72 <= 65536
 #endif
 
 
@@ -94,10 +90,8 @@ struct PrefillCfg {
     static constexpr int kBM = kPrefillBlockM;
     static constexpr int kBN = kPrefillBlockN;
     static constexpr int kNQ = (DPAD <= 128) ? 2 : 1;            // Q tiles per CTA (TMEM budget)
-    static constexpr int kRS = MFA_ROW_SPLIT;                    // softmax threads per query row
-    static constexpr int kSoftmaxWarps = kNQ * 4 * kRS;
+    static constexpr int kSoftmaxWarps = kNQ * 4;                // one thread per query row
     static constexpr int kThreads = (kSoftmaxWarps + 4) * 32;    // + one warpgroup {TMA warp, MMA warp, TMEM warp, spare}
-    static constexpr int kXchgBytes = 2 * 2 * 2 * 128 * 4;       // row-max / row-sum exchange between the two threads of a row
     static constexpr int kSub = DPAD / 64;                       // 64-column (128-byte) sub-tiles per row
     static constexpr int kSubBytes = 128 * 128;                  // 128 rows x 128 B
     static constexpr int kQTileBytes = kSub * kSubBytes;
@@ -109,7 +103,7 @@ struct PrefillCfg {
     static constexpr int kQBytes = kNQ * kQTileBytes;
     static constexpr int kRingBytes = kStages * kKVTileBytes;
     static constexpr int kBarOffset = kQBytes + kRingBytes;
-    static constexpr int kSmemBytes = kBarOffset + 512 + kXchgBytes + 1024;   // barriers + exchange + alignment slack
+    static constexpr int kSmemBytes = kBarOffset + 512 + 1024;   // barriers + alignment slack
     static constexpr uint32_t kTmemCols = 512;
     static constexpr uint32_t kTmemS = 0;                        // S_i at kTmemS + i*128
     static constexpr uint32_t kTmemO = 256;                      // O_i at kTmemO + i*DPAD
@@ -246,11 +240,9 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int total_items = p.num_m_blocks * p.heads * p.batch;
-    constexpr int kRS = Cfg::kRS;
     constexpr int kWarpTma = Cfg::kSoftmaxWarps, kWarpMma = kWarpTma + 1, kWarpTmem = kWarpTma + 2;
-    float* xchg = reinterpret_cast<float*>(smem + Cfg::kBarOffset + 512);   // [2 buffers][2 Q tiles][2 halves][128 rows]
 #ifdef MFA_TRACE
-    const bool tr_cta = p.trace && blockIdx.x == 0 && lane == 0 && (warp == kWarpMma || ((warp & 3) == 0 && (warp / 4) % kRS == 0));
+    const bool tr_cta = p.trace && blockIdx.x == 0 && lane == 0 && (warp == kWarpMma || (warp & 3) == 0);
     bool tr_on = false;
 #endif
 
@@ -514,29 +506,17 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
         }
     }
     } else {
-      asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(Cfg::kThreads == 640 ? MFA_REG_SOFTMAX_640 : MFA_REG_SOFTMAX));
+      asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MFA_REG_SOFTMAX));
       if (warp < Cfg::kSoftmaxWarps) {
         // ======================================================================= softmax warpgroups
-        // warp -> (Q tile i, column half hf, TMEM lane quarter): a warp may only touch TMEM lanes 32 * (warp % 4) ... + 31,
-        // so the two warps that share the rows of a quarter are warp and warp + 4 -- both on the same SM sub-partition
-        const int i = warp / (4 * kRS);
-        const int hf = (warp >> 2) % kRS;                         // 0: key columns 0-63 of a tile (kRS = 2), 1: 64-127
+        // warp -> (Q tile i, TMEM lane quarter): a warp may only touch TMEM lanes 32 * (warp % 4) ... + 31
+        const int i = warp / 4;
         const int row_in_tile = (warp & 3) * 32 + lane;
         const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
         const uint32_t tS = tmem_base + lane_sel + Cfg::kTmemS + i * 128;
         const uint32_t tO = tmem_base + lane_sel + Cfg::kTmemO + i * DPAD;
         const float c2 = p.scale_log2;
         uint32_t t_cnt = 0;   // KV tiles this warpgroup has processed so far (parity base)
-        uint32_t x_cnt = 0;   // row exchanges so far (kRS = 2: double-buffer index of the exchange area)
-        // value exchange between the two threads of a row (one barrier per exchange; 2 buffers: a thread can be at most
-        // one exchange ahead of its partner, who has finished reading buffer b before it arrives at the barrier of b ^ 1)
-        auto row_exchange = [&](float mine) -> float {
-            float* buf = xchg + ((x_cnt & 1u) * 2 + i) * 256;
-            buf[hf * 128 + row_in_tile] = mine;
-            named_bar_sync(1 + i, 128 * kRS);
-            ++x_cnt;
-            return buf[(hf ^ 1) * 128 + row_in_tile];
-        };
         for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
             const PrefillItem w = prefill_item<kNQ>(p, item);
             if (!w.valid) continue;
@@ -572,16 +552,41 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                             if (col0 + cbase + c < lim_lo) a[c] = 0xff800000u;
                     }
                 };
-                // P = exp2(S*c2 - ms), packed FFMA2 for the scale, MUFU.EX2, packed add for the row sum, pack to 16 bit
+                // P = exp2(S*c2 - ms), packed FFMA2 for the scale, MUFU.EX2, packed add for the row sum, pack to 16 bit.
+                // With kPoly every MFA_POLY_EVERY-th pair is computed on the FMA pipe instead of the MUFU (4 lanes per SM
+                // sub-partition, the busiest pipe of this kernel): 2^x = 2^floor(x) * p(x - floor(x)), floor by the
+                // round-down add of 1.5 * 2^23, p the degree-3 minimax polynomial (relative error 8.8e-5, below half an ulp
+                // of fp16 / bf16 P; p(0) = 1), the exponent added to p's bit pattern.  x is clamped to -127 first, so every
+                // finite or -inf score is exact arithmetic from there on (the result of a clamped element is a denormal
+                // ~1e-38 rather than 0 -- which is why masked tiles, whose rows may be masked entirely, keep the MUFU).
                 const uint64_t c2_2 = f2_pack(c2, c2);
-                auto exp64 = [&](const uint32_t (&a)[64], float ms_, uint32_t (&pk)[32], uint64_t (&acc)[2]) {
+                auto exp64 = [&](const uint32_t (&a)[64], float ms_, uint32_t (&pk)[32], uint64_t (&acc)[2], auto poly_tag) {
+                    constexpr bool kPoly = decltype(poly_tag)::value;
                     const uint64_t nms_2 = f2_pack(-ms_, -ms_);
 #pragma unroll
                     for (int c = 0; c < 32; ++c) {
                         const uint64_t x2 = f2_fma(f2_pack(__uint_as_float(a[2 * c]), __uint_as_float(a[2 * c + 1])), c2_2, nms_2);
-                        float x0, x1;
+                        float x0, x1, p0, p1;
                         f2_unpack(x2, x0, x1);
-                        const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
+                        if (kPoly && MFA_POLY_EVERY > 0 && (c % (MFA_POLY_EVERY > 0 ? MFA_POLY_EVERY : 1)) == (MFA_POLY_EVERY - 1)) {
+                            constexpr float kMagic = 12582912.f;   // 1.5 * 2^23: x + kMagic (round down) = kMagic + floor(x)
+                            const uint64_t xc = f2_pack(fmaxf(x0, -127.f), fmaxf(x1, -127.f));
+                            const uint64_t t2 = f2_add_rm(xc, f2_pack(kMagic, kMagic));
+                            const uint64_t fl = f2_add(t2, f2_pack(-kMagic, -kMagic));                 // floor(x), exact
+                            const uint64_t fr = f2_fma(fl, f2_pack(-1.f, -1.f), xc);                    // x - floor(x), exact
+                            uint64_t pl = f2_fma(f2_pack(0.077119089663028717f, 0.077119089663028717f), fr,
+                                                 f2_pack(0.227564394474029541f, 0.227564394474029541f));
+                            pl = f2_fma(pl, fr, f2_pack(0.695146143436431885f, 0.695146143436431885f));
+                            pl = f2_fma(pl, fr, f2_pack(1.f, 1.f));
+                            float t0, t1, q0, q1;
+                            f2_unpack(t2, t0, t1);
+                            f2_unpack(pl, q0, q1);
+                            p0 = __uint_as_float(__float_as_uint(q0) + (__float_as_uint(t0) << 23));   // (kMagic's bits << 23 = 0 mod 2^32)
+                            p1 = __uint_as_float(__float_as_uint(q1) + (__float_as_uint(t1) << 23));
+                        } else {
+                            p0 = ex2_fast(x0);
+                            p1 = ex2_fast(x1);
+                        }
                         acc[c & 1] = f2_add(acc[c & 1], f2_pack(p0, p1));
                         pk[c] = Elem<T>::pack(p0, p1);
                     }
@@ -600,14 +605,14 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     }
                     return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
                 };
-                // lazy rescale of this thread's part of the O row (columns [oc0, oc0 + ocn)) by `factor`: O_i holds
-                // sum_{t<j} P_t V_t; wait for PV(j-1) first.  Must happen before any part of P(j) is released.
-                auto rescale_o = [&](float factor, int oc0, int ocn) {
+                // lazy rescale of this thread's O row by `factor`: O_i holds sum_{t<j} P_t V_t; wait for PV(j-1) first.
+                // Must happen before any part of P(j) is released.
+                auto rescale_o = [&](float factor) {
                     mbar_wait(&o_full[i], par ^ 1u);
                     tc_fence_after();
                     // (16 columns at a time: this rare path runs with the whole S row live in registers)
 #pragma unroll 1
-                    for (int c = oc0; c < oc0 + ocn; c += 16) {
+                    for (int c = 0; c < DPAD; c += 16) {
                         uint32_t o[16];
                         tmem_ld16(tO + c, o);
                         tmem_wait_ld();
@@ -617,82 +622,48 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     }
                 };
                 uint64_t sum2[2] = {0ull, 0ull};
-                float factor;
-                if constexpr (kRS == 2) {
-                    // ---- two threads per row: this one owns key columns [64 hf, 64 hf + 64) of the tile
-                    uint32_t su[64];
-                    tmem_ld32(tS + hf * 64, *reinterpret_cast<uint32_t(*)[32]>(&su[0]));
-                    tmem_ld32(tS + hf * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&su[32]));
+                uint32_t su_lo[64], su_hi[64];
+                tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[0]));
+                tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[32]));
+                const bool unmasked = !(need_mask || need_mask_lo);   // warp-uniform; all but the diagonal / last tiles
+                float tmax;
+                if (unmasked) {
+                    // the second half of the row streams out of TMEM (64 B/clk per sub-partition) under the max of the first:
+                    // one basic block, no mask code in between (measured: the max phase 472 -> 295 cycles, +2.4 %)
                     tmem_wait_ld();
+                    tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[0]));
+                    tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[32]));
                     MFA_TR(i, j, 2);
-                    mask64(su, hf * 64);
-                    const float my_max = max64(su);
-                    MFA_TR(i, j, 6);
-                    // The exchange is also the point behind which P may overwrite S: the partner has its S columns in
-                    // registers (P of the second half lands on columns 32-63 of the tile, which belong to the first).
-                    const float tmax = fmaxf(my_max, row_exchange(my_max));
-                    const float m_new = fmaxf(m_run, tmax);
-                    // lazy rescale: keep the stale max unless it grew by more than 2^8 (both threads of a row decide alike)
-                    const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
-                    const float m_use = grow ? m_new : m_run;
-                    factor = grow ? ((m_run == -INFINITY) ? 0.f : exp2f((m_run - m_new) * c2)) : 1.f;
-                    const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
-                    m_run = m_use;
-                    const bool any_grow = __any_sync(0xffffffffu, grow);
-                    MFA_TR(i, j, 7);
-                    if (j > j_first && any_grow) rescale_o(factor, hf * (DPAD / 2), DPAD / 2);
-                    MFA_TR(i, j, 3);
-                    {   // (two stores of 16 packed columns: the S registers die as they are consumed, the budget is 104)
-                        const uint64_t nms_2 = f2_pack(-ms, -ms);
-#pragma unroll
-                        for (int k = 0; k < 2; ++k) {
-                            uint32_t pk[16];
-#pragma unroll
-                            for (int c = 0; c < 16; ++c) {
-                                const int e = 32 * k + 2 * c;
-                                const uint64_t x2 = f2_fma(f2_pack(__uint_as_float(su[e]), __uint_as_float(su[e + 1])), c2_2, nms_2);
-                                float x0, x1;
-                                f2_unpack(x2, x0, x1);
-                                const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
-                                sum2[c & 1] = f2_add(sum2[c & 1], f2_pack(p0, p1));
-                                pk[c] = Elem<T>::pack(p0, p1);
-                            }
-                            tmem_st16(tS + hf * 32 + k * 16, pk);
-                        }
-                    }
-                    tmem_wait_st();
-                    tc_fence_before();
-                    mbar_arrive(hf == 0 ? &p_lo[i] : &p_hi[i]);   // (each half of P comes from its own 128 threads)
-                    MFA_TR(i, j, 4 + hf);
+                    const float tmax_lo = max64(su_lo);
+                    tmem_wait_ld();
+                    tmax = fmaxf(tmax_lo, max64(su_hi));
                 } else {
-                    // ---- one thread per row
-                    uint32_t su_lo[64], su_hi[64];
-                    tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[0]));
-                    tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&su_lo[32]));
                     tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[0]));
                     tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[32]));
                     tmem_wait_ld();
                     MFA_TR(i, j, 2);
                     mask64(su_lo, 0);
                     mask64(su_hi, 64);
-                    const float tmax = fmaxf(max64(su_lo), max64(su_hi));
-                    MFA_TR(i, j, 6);
-                    const float m_new = fmaxf(m_run, tmax);
-                    // lazy rescale: keep the stale max unless it grew by more than 2^8
-                    const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
-                    const float m_use = grow ? m_new : m_run;
-                    factor = grow ? ((m_run == -INFINITY) ? 0.f : exp2f((m_run - m_new) * c2)) : 1.f;
-                    const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
-                    m_run = m_use;
-                    const bool any_grow = __any_sync(0xffffffffu, grow);
-                    MFA_TR(i, j, 7);
-                    if (j > j_first && any_grow) rescale_o(factor, 0, DPAD);
-                    MFA_TR(i, j, 3);
-                    // P is released to the MMA warp in two halves so that P.V k-steps 0-3 run while the second half is still
-                    // being exponentiated
+                    tmax = fmaxf(max64(su_lo), max64(su_hi));
+                }
+                MFA_TR(i, j, 6);
+                const float m_new = fmaxf(m_run, tmax);
+                // lazy rescale: keep the stale max unless it grew by more than 2^8
+                const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
+                const float m_use = grow ? m_new : m_run;
+                const float factor = grow ? ((m_run == -INFINITY) ? 0.f : exp2f((m_run - m_new) * c2)) : 1.f;
+                const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
+                m_run = m_use;
+                const bool any_grow = __any_sync(0xffffffffu, grow);
+                MFA_TR(i, j, 7);
+                if (j > j_first && any_grow) rescale_o(factor);
+                MFA_TR(i, j, 3);
+                // P is released to the MMA warp in two halves so that P.V k-steps 0-3 run while the second half is still
+                // being exponentiated
+                auto release_halves = [&](auto poly_tag) {
                     {
                         uint32_t pk0[32];
-                        exp64(su_lo, ms, pk0, sum2);
+                        exp64(su_lo, ms, pk0, sum2, poly_tag);
                         tmem_st32(tS, pk0);
                         tmem_wait_st();
                         tc_fence_before();
@@ -701,14 +672,18 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     }
                     {
                         uint32_t pk1[32];
-                        exp64(su_hi, ms, pk1, sum2);
+                        exp64(su_hi, ms, pk1, sum2, poly_tag);
                         tmem_st32(tS + 32, pk1);
                         tmem_wait_st();
                         tc_fence_before();
                         mbar_arrive(&p_hi[i]);
                         MFA_TR(i, j, 5);
                     }
-                }
+                };
+                if (MFA_POLY_EVERY > 0 && unmasked)
+                    release_halves(std::true_type{});
+                else
+                    release_halves(std::false_type{});
                 float sa, sb, sc, sd;
                 f2_unpack(sum2[0], sa, sb);
                 f2_unpack(sum2[1], sc, sd);
@@ -726,16 +701,13 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     mbar_wait(&o_full[i], (t_cnt + (uint32_t)n_mine - 1u) & 1u);
                     tc_fence_after();
                 }
-                // (two threads per row: each holds the sum over its own key columns)
-                const float l_row = (kRS == 2) ? l_run + row_exchange(l_run) : l_run;
+                const float l_row = l_run;
                 const float inv = (l_row == 0.f || l_row != l_row) ? 1.f : 1.f / l_row;   // prefill.cuh:604-605
-                if (p.lse != nullptr && row_ok && hf == 0)   // natural-log LSE of the scaled scores (the reference drops it, api.cpp:436)
+                if (p.lse != nullptr && row_ok)   // natural-log LSE of the scaled scores (the reference drops it, api.cpp:436)
                     p.lse[(int64_t)w.b * p.lse_batch_stride + (int64_t)w.h * p.lse_head_stride + w.q_off + qrow] =
                         (l_row == 0.f || l_row != l_row) ? -INFINITY : (m_run * c2 + log2f(l_row)) * 0.6931471805599453f;
-                constexpr int kChunks = DPAD / 32 / kRS;   // 32-column chunks of the O row per thread
 #pragma unroll
-                for (int c0 = 0; c0 < kChunks; ++c0) {
-                    const int c = hf * kChunks + c0;
+                for (int c = 0; c < DPAD / 32; ++c) {
                     uint32_t o[32];
                     if (n_mine > 0) {   // warp-uniform
                         tmem_ld32(tO + c * 32, o);

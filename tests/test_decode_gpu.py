@@ -182,12 +182,12 @@ def test_lse_and_partial_merge_matches_full(mfa):
     kc, vc, _ = _cache(B, KV, Hkv, D, None, torch.float16, g)
     ref, lse_ref = R.kvcache_ref(q, kc, vc, None, return_lse=True)
     parts = []
-    for a, b in ((0, 1024), (1024, 1024), (1024, 3000)):  # the middle shard is empty
+    for a, b in ((0, 1024), (1024, 1024), (1024, 3000)):  # the middle shard is empty: O = 0, LSE = -inf, no launch
+        o, l = _C.decode_partial(q, kc[:, a:b], vc[:, a:b], None, None, 0)
         if a == b:
-            o = torch.zeros(B, H, D, device="cuda")
-            l = torch.full((B, H), float("-inf"), device="cuda")
-        else:
-            o, l = _C.decode_partial(q, kc[:, a:b], vc[:, a:b], None, None, 0)
+            assert o.shape == (B, H, D) and not o.any() and torch.isneginf(l).all()
+            o2, l2 = _C._py_decode_partial(q, kc[:, a:b], vc[:, a:b], None, None, 0)
+            assert not o2.any() and torch.isneginf(l2).all()
         parts.append(torch.cat([o, l[..., None]], dim=-1).reshape(B * H, D + 1))
     o, l = _C.decode_partial(q, kc, vc, None, None, 0)
     assert (l - lse_ref).abs().max().item() < 1e-3
