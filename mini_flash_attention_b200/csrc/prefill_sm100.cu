@@ -30,7 +30,6 @@
 // kv_head = head / group (:49); varlen through cu_seqlens (:19-33); paged K/V through block_table --
 // gathered per page box, not per 64-row tile (fixes quirk Q3 of SURVEY.md).
 #include <cstdlib>
-#include <type_traits>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -41,10 +40,6 @@
 // threads.  setmaxnreg only moves registers INSIDE the pool the CTA was launched with -- 168 registers x 384 threads =
 // 64512, not the SM's 65536 -- so 256 * SOFTMAX + 128 * HELPER must be <= 64512 (216 / 72 is exact; a split that needs
 // more blocks in setmaxnreg.inc for ever).
-// Every MFA_POLY_EVERY-th pair of exponentials of an unmasked tile goes to the FMA pipe as a polynomial (0 = none).
-#ifndef MFA_POLY_EVERY
-#define MFA_POLY_EVERY 0
-#endif
 #ifndef MFA_REG_SOFTMAX
 #define MFA_REG_SOFTMAX 216
 #endif
@@ -56,10 +51,15 @@
 #ifdef MFA_TRACE
 #define MFA_TR(role, it, ev)                                                                              \
     do {                                                                                                  \
-        if (tr_on && (it) < 64) p.trace[((role) * 64 + (it)) * 8 + (ev)] = clock64();                      \
+        if (tr_on && tr_base + (it) < 64) p.trace[((role) * 64 + tr_base + (it)) * 8 + (ev)] = clock64();  \
+    } while (0)
+#define MFA_TRI(role, ev)                                                                                  \
+    do {                                                                                                  \
+        if (tr_on && tr_item < 64) p.trace[((role) * 64 + tr_item) * 8 + (ev)] = clock64();                \
     } while (0)
 #else
 #define MFA_TR(role, it, ev) do { } while (0)
+#define MFA_TRI(role, ev) do { } while (0)
 #endif
 
 namespace mfa {
@@ -242,8 +242,10 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
     const int total_items = p.num_m_blocks * p.heads * p.batch;
     constexpr int kWarpTma = Cfg::kSoftmaxWarps, kWarpMma = kWarpTma + 1, kWarpTmem = kWarpTma + 2;
 #ifdef MFA_TRACE
-    const bool tr_cta = p.trace && blockIdx.x == 0 && lane == 0 && (warp == kWarpMma || (warp & 3) == 0);
+    const bool tr_cta = p.trace && blockIdx.x == 0 && lane == 0 && (warp == kWarpMma || warp == kWarpTma || (warp < kWarpTma && (warp & 3) == 0));
     bool tr_on = false;
+    int tr_base = 0;   // running KV-step index of this role over the CTA's items (the trace covers the first 64 steps)
+    int tr_item = 0;   // items done by this role
 #endif
 
     // ---- one-time setup
@@ -298,6 +300,10 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             if (!w.valid) continue;
             const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
             const int q_b_coord = p.cu_seqlens_q ? 0 : w.b;
+#ifdef MFA_TRACE
+            tr_on = tr_cta;
+#endif
+            MFA_TRI(3, 4);   // producer reaches the item
             // Q tiles of this item -- only the tiles that have KV work (n_i > 0).  A tile without work is never read by
             // an MMA, so loading it would leave a bulk copy in flight that nobody awaits (it could land after the CTA
             // exited, or be re-armed before it landed).  q_full / q_empty phases therefore count LOADS of tile i
@@ -317,6 +323,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 __syncwarp();
                 ++q_ld[i];
             }
+            MFA_TRI(3, 5);   // Q loads issued
             const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
             const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
             // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
@@ -358,6 +365,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                         }
                     }
                     __syncwarp();
+                    if (j == w.j_lo && kv == 0) MFA_TRI(3, 6);   // first K load of the item issued
                     if (fix) {
                         // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
                         mbar_wait(tail_bar, tail_phase);
@@ -373,6 +381,10 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     }
                 }
             }
+            MFA_TRI(3, 7);   // last load of the item issued
+#ifdef MFA_TRACE
+            ++tr_item;
+#endif
         }
     } else if (warp == kWarpMma) {
         // ======================================================================= MMA issuer
@@ -444,7 +456,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 const PrefillItem w = prefill_item<kNQ>(p, item);
                 if (!w.valid) continue;
 #ifdef MFA_TRACE
-                tr_on = tr_cta && item == (int)blockIdx.x;
+                tr_on = tr_cta;
 #endif
                 const int n_max = w.n_max;
 #pragma unroll
@@ -455,6 +467,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     mbar_wait(&kv_full[sK], (it / kStages) & 1);
                     ++it;
                     tc_fence_after();
+                    MFA_TR(2, 0, 7);   // Q tiles and K(first) of the item landed
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i)
                         if (w.active(i, w.j_lo)) {
@@ -475,7 +488,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                         ++it;
                     }
                     tc_fence_after();
-                    MFA_TR(2, j, 0);
+                    MFA_TR(2, j - w.j_lo, 0);
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i) {
                         if (w.active(i, j)) {
@@ -484,24 +497,27 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                             // previous item's epilogue -- its TMEM reads of O_i included -- before it released this P)
                             mbar_wait(&p_lo[i], par);
                             tc_fence_after();
-                            MFA_TR(2, j, 1 + 3 * i);
+                            MFA_TR(2, j - w.j_lo, 1 + 3 * i);
                             issue_PV(i, sV, j > w.lo_i[i], 0, kBN / 32, false);
                             mbar_wait(&p_hi[i], par);
                             tc_fence_after();
-                            MFA_TR(2, j, 2 + 3 * i);
+                            MFA_TR(2, j - w.j_lo, 2 + 3 * i);
                             issue_PV(i, sV, j > w.lo_i[i], kBN / 32, kBN / 16, true);
                         }
                         if (w.active(i, j + 1)) {
                             issue_S(i, sK);
                             release_q(w, i, j + 1);
                         }
-                        MFA_TR(2, j, 3 + 3 * i);
+                        MFA_TR(2, j - w.j_lo, 3 + 3 * i);
                     }
                     commit(&kv_empty[sV]);
                     if (has_next) commit(&kv_empty[sK]);
                 }
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i) t_cnt[i] += (uint32_t)w.count(i);
+#ifdef MFA_TRACE
+                tr_base += n_max - w.j_lo;
+#endif
             }
         }
     }
@@ -521,7 +537,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             const PrefillItem w = prefill_item<kNQ>(p, item);
             if (!w.valid) continue;
 #ifdef MFA_TRACE
-            tr_on = tr_cta && item == (int)blockIdx.x;
+            tr_on = tr_cta;
 #endif
             const int m0 = w.m0, len_k = w.len_k, len_q = w.len_q;
             const int qrow = m0 + i * kBM + row_in_tile;            // row inside the sequence
@@ -531,10 +547,10 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
 
             for (int j = j_first; j < w.n_i[i]; ++j) {
                 const uint32_t par = (t_cnt + (uint32_t)(j - j_first)) & 1u;
-                MFA_TR(i, j, 0);
+                MFA_TR(i, j - j_first, 0);
                 mbar_wait(&s_full[i], par);
                 tc_fence_after();
-                MFA_TR(i, j, 1);
+                MFA_TR(i, j - j_first, 1);
                 const int col0 = j * kBN;
                 const bool need_mask = (col0 + kBN > len_k) || (p.has_hi && (col0 + kBN - 1 > m0 + i * kBM + w.shift_hi));
                 const bool need_mask_lo = p.has_lo && col0 < m0 + i * kBM + kBM - 1 + w.shift_lo;   // the tile's last row has the largest bound
@@ -553,40 +569,19 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     }
                 };
                 // P = exp2(S*c2 - ms), packed FFMA2 for the scale, MUFU.EX2, packed add for the row sum, pack to 16 bit.
-                // With kPoly every MFA_POLY_EVERY-th pair is computed on the FMA pipe instead of the MUFU (4 lanes per SM
-                // sub-partition, the busiest pipe of this kernel): 2^x = 2^floor(x) * p(x - floor(x)), floor by the
-                // round-down add of 1.5 * 2^23, p the degree-3 minimax polynomial (relative error 8.8e-5, below half an ulp
-                // of fp16 / bf16 P; p(0) = 1), the exponent added to p's bit pattern.  x is clamped to -127 first, so every
-                // finite or -inf score is exact arithmetic from there on (the result of a clamped element is a denormal
-                // ~1e-38 rather than 0 -- which is why masked tiles, whose rows may be masked entirely, keep the MUFU).
+                // (Every exponential on the MUFU: moving a share of them to the FMA pipe as a degree-3 polynomial, the
+                // FlashAttention-4 trick, was measured twice -- round 1 and again in round 2 with 1/8 ... 1/2 of the pairs --
+                // and never won: this warp is alone on its sub-partition for the whole phase and issues ~1 instruction per
+                // 2.3 cycles, so the ~10 extra FMA-pipe instructions per pair cost what the saved MUFU slots return.)
                 const uint64_t c2_2 = f2_pack(c2, c2);
-                auto exp64 = [&](const uint32_t (&a)[64], float ms_, uint32_t (&pk)[32], uint64_t (&acc)[2], auto poly_tag) {
-                    constexpr bool kPoly = decltype(poly_tag)::value;
+                auto exp64 = [&](const uint32_t (&a)[64], float ms_, uint32_t (&pk)[32], uint64_t (&acc)[2]) {
                     const uint64_t nms_2 = f2_pack(-ms_, -ms_);
 #pragma unroll
                     for (int c = 0; c < 32; ++c) {
                         const uint64_t x2 = f2_fma(f2_pack(__uint_as_float(a[2 * c]), __uint_as_float(a[2 * c + 1])), c2_2, nms_2);
-                        float x0, x1, p0, p1;
+                        float x0, x1;
                         f2_unpack(x2, x0, x1);
-                        if (kPoly && MFA_POLY_EVERY > 0 && (c % (MFA_POLY_EVERY > 0 ? MFA_POLY_EVERY : 1)) == (MFA_POLY_EVERY - 1)) {
-                            constexpr float kMagic = 12582912.f;   // 1.5 * 2^23: x + kMagic (round down) = kMagic + floor(x)
-                            const uint64_t xc = f2_pack(fmaxf(x0, -127.f), fmaxf(x1, -127.f));
-                            const uint64_t t2 = f2_add_rm(xc, f2_pack(kMagic, kMagic));
-                            const uint64_t fl = f2_add(t2, f2_pack(-kMagic, -kMagic));                 // floor(x), exact
-                            const uint64_t fr = f2_fma(fl, f2_pack(-1.f, -1.f), xc);                    // x - floor(x), exact
-                            uint64_t pl = f2_fma(f2_pack(0.077119089663028717f, 0.077119089663028717f), fr,
-                                                 f2_pack(0.227564394474029541f, 0.227564394474029541f));
-                            pl = f2_fma(pl, fr, f2_pack(0.695146143436431885f, 0.695146143436431885f));
-                            pl = f2_fma(pl, fr, f2_pack(1.f, 1.f));
-                            float t0, t1, q0, q1;
-                            f2_unpack(t2, t0, t1);
-                            f2_unpack(pl, q0, q1);
-                            p0 = __uint_as_float(__float_as_uint(q0) + (__float_as_uint(t0) << 23));   // (kMagic's bits << 23 = 0 mod 2^32)
-                            p1 = __uint_as_float(__float_as_uint(q1) + (__float_as_uint(t1) << 23));
-                        } else {
-                            p0 = ex2_fast(x0);
-                            p1 = ex2_fast(x1);
-                        }
+                        const float p0 = ex2_fast(x0), p1 = ex2_fast(x1);
                         acc[c & 1] = f2_add(acc[c & 1], f2_pack(p0, p1));
                         pk[c] = Elem<T>::pack(p0, p1);
                     }
@@ -633,7 +628,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     tmem_wait_ld();
                     tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[0]));
                     tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[32]));
-                    MFA_TR(i, j, 2);
+                    MFA_TR(i, j - j_first, 2);
                     const float tmax_lo = max64(su_lo);
                     tmem_wait_ld();
                     tmax = fmaxf(tmax_lo, max64(su_hi));
@@ -641,12 +636,12 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[0]));
                     tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&su_hi[32]));
                     tmem_wait_ld();
-                    MFA_TR(i, j, 2);
+                    MFA_TR(i, j - j_first, 2);
                     mask64(su_lo, 0);
                     mask64(su_hi, 64);
                     tmax = fmaxf(max64(su_lo), max64(su_hi));
                 }
-                MFA_TR(i, j, 6);
+                MFA_TR(i, j - j_first, 6);
                 const float m_new = fmaxf(m_run, tmax);
                 // lazy rescale: keep the stale max unless it grew by more than 2^8
                 const bool grow = (m_new - m_run) * c2 > Cfg::kRescaleThreshold;   // also true when m_run == -inf
@@ -655,35 +650,29 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 const float ms = (m_use == -INFINITY) ? 0.f : m_use * c2;
                 m_run = m_use;
                 const bool any_grow = __any_sync(0xffffffffu, grow);
-                MFA_TR(i, j, 7);
+                MFA_TR(i, j - j_first, 7);
                 if (j > j_first && any_grow) rescale_o(factor);
-                MFA_TR(i, j, 3);
+                MFA_TR(i, j - j_first, 3);
                 // P is released to the MMA warp in two halves so that P.V k-steps 0-3 run while the second half is still
                 // being exponentiated
-                auto release_halves = [&](auto poly_tag) {
-                    {
-                        uint32_t pk0[32];
-                        exp64(su_lo, ms, pk0, sum2, poly_tag);
-                        tmem_st32(tS, pk0);
-                        tmem_wait_st();
-                        tc_fence_before();
-                        mbar_arrive(&p_lo[i]);
-                        MFA_TR(i, j, 4);
-                    }
-                    {
-                        uint32_t pk1[32];
-                        exp64(su_hi, ms, pk1, sum2, poly_tag);
-                        tmem_st32(tS + 32, pk1);
-                        tmem_wait_st();
-                        tc_fence_before();
-                        mbar_arrive(&p_hi[i]);
-                        MFA_TR(i, j, 5);
-                    }
-                };
-                if (MFA_POLY_EVERY > 0 && unmasked)
-                    release_halves(std::true_type{});
-                else
-                    release_halves(std::false_type{});
+                {
+                    uint32_t pk0[32];
+                    exp64(su_lo, ms, pk0, sum2);
+                    tmem_st32(tS, pk0);
+                    tmem_wait_st();
+                    tc_fence_before();
+                    mbar_arrive(&p_lo[i]);
+                    MFA_TR(i, j - j_first, 4);
+                }
+                {
+                    uint32_t pk1[32];
+                    exp64(su_hi, ms, pk1, sum2);
+                    tmem_st32(tS + 32, pk1);
+                    tmem_wait_st();
+                    tc_fence_before();
+                    mbar_arrive(&p_hi[i]);
+                    MFA_TR(i, j - j_first, 5);
+                }
                 float sa, sb, sc, sd;
                 f2_unpack(sum2[0], sa, sb);
                 f2_unpack(sum2[1], sc, sd);
@@ -697,10 +686,12 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 T* orow = static_cast<T*>(p.o) + (int64_t)w.h * p.o_head_stride +
                           (p.cu_seqlens_q ? (int64_t)(w.q_off + qrow) * p.o_row_stride
                                           : (int64_t)w.b * p.o_batch_stride + (int64_t)qrow * p.o_row_stride);
+                MFA_TRI(3 + i, 0);
                 if (n_mine > 0) {
                     mbar_wait(&o_full[i], (t_cnt + (uint32_t)n_mine - 1u) & 1u);
                     tc_fence_after();
                 }
+                MFA_TRI(3 + i, 1);
                 const float l_row = l_run;
                 const float inv = (l_row == 0.f || l_row != l_row) ? 1.f : 1.f / l_row;   // prefill.cuh:604-605
                 if (p.lse != nullptr && row_ok)   // natural-log LSE of the scaled scores (the reference drops it, api.cpp:436)
@@ -731,7 +722,12 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     }
                 }
             }
+            MFA_TRI(3 + i, 2);
             t_cnt += (uint32_t)n_mine;
+#ifdef MFA_TRACE
+            tr_base += n_mine;
+            ++tr_item;
+#endif
         }
       }
     }

@@ -4,6 +4,7 @@
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+import statistics
 import torch
 import mini_flash_attention as mfa
 from mini_flash_attention_b200 import _lib
@@ -26,6 +27,23 @@ print("softmax events: 0 loop top, 1 S ready, 2 S in regs, 6 row max done, 7 gro
 print("mma events (single): 0 K/V ready, 1 p_lo0 seen, 2 p_hi0 seen, 3 PV0+S0 issued, 4 p_lo1 seen, 5 p_hi1 seen, 6 PV1+S1 issued")
 print("mma events (pair): 0 K(j+1) ready, 4 S(j+1) issued, 5 V(j) ready, 1 p_lo seen, 2 p_hi seen (PV lo issued), 3 PV hi issued")
 n = min(S // 128, 64)
+if S <= 2048:
+    # short sequences: the trace runs over the first 64 KV steps of CTA 0, i.e. several items; show the item boundaries
+    ep = buf.cpu()[3 * 64 * 8:5 * 64 * 8].view(2, 64, 8)
+    print(f"item timeline (S={S}: {n} KV steps per item); all times relative to the first stamp")
+    print("  prod: reaches item / Q issued / first K issued / last load issued;  MMA: Q+K landed;  WGi: first S ready, last P released, o_full seen, epilogue done")
+    for k in range(min(64 // n, 12)):
+        b = k * n
+        line = f"  item {k:2d} prod {[r(ep[0, k, e]) for e in (4, 5, 6, 7)]} MMA start {r(t[2, b, 7])}"
+        for i in (0, 1):
+            line += f"  WG{i} [{r(t[i, b, 1])}, {r(t[i, b + n - 1, 5])}, {r(ep[i, k, 1])}, {r(ep[i, k, 2])}]"
+        print(line)
+    for i in (0, 1):
+        d = [int(t[i, (k + 1) * n, 1] - t[i, k * n, 1]) for k in range(1, min(64 // n, 12) - 1)]
+        print(f"  WG{i} item period median {statistics.median(d)}  (= {n} steps x {statistics.median(d) / n:.0f}); steady-state step from long sequences ~3440")
+        gap = [int(t[i, (k + 1) * n, 1] - t[i, k * n + n - 1, 5]) for k in range(1, min(64 // n, 12) - 1)]
+        print(f"  WG{i} last P released -> next item's first S ready: median {statistics.median(gap)}")
+    sys.exit(0)
 for j in list(range(0, 6)) + list(range(n - 3, n)):
     print(f"j={j:2d} WG0 {[r(x) for x in t[0, j, :8]]}  WG1 {[r(x) for x in t[1, j, :8]]}  MMA {[r(x) for x in t[2, j, :8]]}")
 import statistics
