@@ -20,12 +20,12 @@
 namespace mfa {
 cudaError_t launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeKParams& p, bool is_bf16,
                           int dpad, cudaStream_t stream);
-cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream);
+cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream, bool dependent);
 cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                            const PrefillKParams& p, bool is_bf16, int dpad, cudaStream_t stream);
 int prefill_rows_per_cta(int dpad);
 cudaError_t launch_kvcache_append(const mfa_append_params_t& p, int sm_count, cudaStream_t stream);
-cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream);
+cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream, bool dependent);
 }  // namespace mfa
 
 // Exchange buffer of the KV-sharded decode (include/mfa_b200.h; kernel in xchg_sm100.cu).  One cudaMalloc per rank:
@@ -247,32 +247,24 @@ static int decode_splits_for(const mfa_params_t* p) {
     const int num_n_blocks = std::max(1, (p->seqlen_k + block_n - 1) / block_n);
     int splits = p->num_splits;
     if (splits < 1) {
-        // Heuristic in the spirit of api.cpp:269-302, re-derived for this kernel: one CTA serves a whole GQA
-        // group, two CTAs per SM are planned for (see above), and a split should keep >= 4 tiles (256 rows) of work.
+        // Heuristic in the place of api.cpp:269-302, fitted to this kernel (scripts/decode_splits_gqa.py, L2-cold sweep,
+        // profiles/decode_splits_r02b.txt): one CTA serves a whole GQA group and two CTAs per SM are resident.  Splitting
+        // pays only while ALL items still run as ONE wave (every extra item of a persistent CTA repeats the ~3 us ramp,
+        // and the merge costs a few us), and only with >= 8 tiles (512 rows) per split:
+        //   splits = min(slots / items_unsplit, tiles / 8).
+        // B=24 GQA 32/8 (192 items) and B=24 MHA (576) stay unsplit at every KV length (KV=2048: 38 us unsplit vs 43-47
+        // split); B=8 GQA KV=4096 takes 4 splits (29.9 us vs 52.5 unsplit and 38.6 with the 9 splits the wave-efficiency
+        // rule of round 1 chose); a B=1 long-context step takes 37.
         const int group = p->heads / p->kv_heads;
         const int head_tiles = (group + mfa::kDecodeMaxGroup - 1) / mfa::kDecodeMaxGroup;
-        const int base = p->batch * p->kv_heads * head_tiles;
+        const int base = std::max(1, p->batch * p->kv_heads * head_tiles);
         const int slots = MFA_DECODE_CTAS_PER_SM * sm_count();
-        // No split when the grid already fills 80 % of the slots -- or has at least one CTA per SM and a short KV axis:
-        // one CTA keeps 64 KB in flight, which is enough to pull an SM's share of HBM, so B=24 GQA 32/8 (192 CTAs on
-        // 148 SMs) is already within ~10 % of the HBM time unsplit, and the split form only adds the merge launch
-        // (scripts/decode_splits_gqa.py: KV=1024 20.5 us unsplit vs 27.0 with 3 splits, 2048: 38.9 vs 45.2, 4096: 69.7 vs 72.2).
-        if (base * 10 >= slots * 8 || (base >= sm_count() && num_n_blocks <= 64)) {
-            splits = 1;
-        } else {
-            const int max_splits = std::min({128, std::max(1, num_n_blocks / 4), num_n_blocks});
-            float best_eff = 0.f;
-            int best = 1;
-            for (int s = 1; s <= max_splits; ++s) {
-                const float waves = (float)(base * s) / (float)slots;
-                const float eff = waves / std::ceil(waves);
-                if (eff > best_eff + 1e-6f) {
-                    best_eff = eff;
-                    best = s;
-                }
-                if (eff >= 0.9f && base * s >= slots) break;
-            }
-            splits = best;
+        splits = std::max(1, std::min({slots / base, num_n_blocks / 8, 128}));
+        // A partly filled single wave of LONG items (B=24 GQA at KV=8192: 192 items on 296 slots) gains ~3 % from being
+        // cut into two full waves (3 splits of 43 tiles: 125.9 us vs 129.9); at 4096 rows it already loses (71.3 vs 68.5).
+        if (splits == 1 && 2 * base > slots && base < slots) {
+            const int two_waves = (2 * slots) / base;
+            if (two_waves > 1 && num_n_blocks / two_waves >= 40) splits = two_waves;
         }
     }
     return std::max(1, std::min(splits, num_n_blocks));   // api.cpp:325-327
@@ -428,6 +420,8 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
     kp.k_scale = fp8 ? p->k_scale_ptr : nullptr;
     kp.v_scale = fp8 ? p->v_scale_ptr : nullptr;
 
+    // the merge kernel behind a split launch is a programmatic dependent of it (MFA_DECODE_NO_PDL=1: plain stream order)
+    static const bool use_pdl = [] { const char* e = getenv("MFA_DECODE_NO_PDL"); return !(e && e[0] == '1'); }();
     cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
     cudaError_t e = mfa::launch_decode(tmK, tmV, kp, bf16, dpad, stream);
     if (e != cudaSuccess) return cuda_fail(e, "decode launch");
@@ -454,7 +448,7 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
         xp.max_rows = x->max_rows;
         xp.head_dim = D;
         xp.heads = p->heads;
-        e = mfa::launch_xchg_merge(xp, bf16, stream);
+        e = mfa::launch_xchg_merge(xp, bf16, stream, use_pdl);
         if (e != cudaSuccess) return cuda_fail(e, "exchange-merge launch");
         g_launches.fetch_add(1);
         return MFA_OK;
@@ -473,7 +467,7 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
         cp.rows = (int)rows;
         cp.head_dim = D;
         cp.packed = 0;
-        e = mfa::launch_combine(cp, bf16, stream);
+        e = mfa::launch_combine(cp, bf16, stream, use_pdl);
         if (e != cudaSuccess) return cuda_fail(e, "combine launch");
         g_launches.fetch_add(1);
     }
@@ -648,7 +642,7 @@ int mfa_combine_partials(const float* packed, int num_partials, int rows, int he
     cp.rows = rows;
     cp.head_dim = head_dim;
     cp.packed = 1;
-    cudaError_t e = mfa::launch_combine(cp, is_bf16 != 0, static_cast<cudaStream_t>(cuda_stream));
+    cudaError_t e = mfa::launch_combine(cp, is_bf16 != 0, static_cast<cudaStream_t>(cuda_stream), false);
     if (e != cudaSuccess) return cuda_fail(e, "combine launch");
     g_launches.fetch_add(1);
     return MFA_OK;

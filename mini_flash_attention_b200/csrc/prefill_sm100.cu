@@ -103,7 +103,8 @@ struct PrefillCfg {
     static constexpr int kQBytes = kNQ * kQTileBytes;
     static constexpr int kRingBytes = kStages * kKVTileBytes;
     static constexpr int kBarOffset = kQBytes + kRingBytes;
-    static constexpr int kSmemBytes = kBarOffset + 512 + 1024;   // barriers + alignment slack
+    static constexpr int kOStageWarpBytes = 32 * 128;            // epilogue: 32 rows x 64 columns of 16-bit output per softmax warp
+    static constexpr int kSmemBytes = kBarOffset + 512 + kSoftmaxWarps * kOStageWarpBytes + 1024;   // barriers, output staging, alignment slack
     static constexpr uint32_t kTmemCols = 512;
     static constexpr uint32_t kTmemS = 0;                        // S_i at kTmemS + i*128
     static constexpr uint32_t kTmemO = 256;                      // O_i at kTmemO + i*DPAD
@@ -309,9 +310,11 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             // exited, or be re-armed before it landed).  q_full / q_empty phases therefore count LOADS of tile i
             // (q_ld[i]), not items: every load is awaited by the MMA warp before it commits q_empty, and the producer
             // observes that commit before the next load, so neither barrier ever runs more than one phase ahead.
-#pragma unroll
-            for (int i = 0; i < kNQ; ++i) {
-                if (w.n_i[i] == 0) continue;
+            // Order: Q tile 0, the item's first K tile, Q tile 1, the rest -- tile 0's buffer is free half a period before
+            // tile 1's (their chains interleave), and with its Q and K(first) in flight early tile 0 starts the item
+            // while tile 1 is still finishing the previous one.
+            auto load_q = [&](int i) {
+                if (w.n_i[i] == 0) return;
                 if (q_ld[i] > 0) mbar_wait(&q_empty[i], (q_ld[i] - 1) & 1);
                 if (elect_one()) {
                     mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
@@ -322,8 +325,12 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 }
                 __syncwarp();
                 ++q_ld[i];
-            }
-            MFA_TRI(3, 5);   // Q loads issued
+            };
+            load_q(0);
+#ifdef MFA_Q_TOGETHER   // A/B switch: the round-1 order (both Q tiles first, both awaited at the top of the item)
+            if constexpr (kNQ > 1) load_q(1);
+#endif
+            MFA_TRI(3, 5);   // Q tile 0 issued
             const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
             const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
             // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
@@ -365,7 +372,12 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                         }
                     }
                     __syncwarp();
-                    if (j == w.j_lo && kv == 0) MFA_TRI(3, 6);   // first K load of the item issued
+                    if (j == w.j_lo && kv == 0) {
+                        MFA_TRI(3, 6);   // first K load of the item issued
+#ifndef MFA_Q_TOGETHER
+                        if constexpr (kNQ > 1) load_q(1);
+#endif
+                    }
                     if (fix) {
                         // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
                         mbar_wait(tail_bar, tail_phase);
@@ -452,25 +464,48 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             // a tile by key columns over both warpgroups.
             int it = 0;                   // K/V ring position, runs across items
             uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
+            // The descriptor of the NEXT item (a handful of integer divisions, ~1000 cycles of dependent latency for a lone
+            // warp) is computed while this warp waits for the last P of the current one, not between the items.
+            PrefillItem w_next = prefill_item<kNQ>(p, blockIdx.x);
             for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-                const PrefillItem w = prefill_item<kNQ>(p, item);
-                if (!w.valid) continue;
+                const PrefillItem w = w_next;
+                const int nxt = item + (int)gridDim.x;
+                if (!w.valid) {
+                    if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+                    continue;
+                }
 #ifdef MFA_TRACE
                 tr_on = tr_cta;
 #endif
                 const int n_max = w.n_max;
+                // Q tile i is awaited right in front of ITS first S MMA of the item, not at the top of the item: tile 0 of
+                // the next item starts as soon as its own Q (reloaded when tile 0's last S MMA finished, half a period
+                // before tile 1's) and the first K tile are there.
+                bool q_seen[kNQ];
+#pragma unroll
+                for (int i = 0; i < kNQ; ++i) q_seen[i] = false;
+                auto await_q = [&](int i) {
+                    if (!q_seen[i]) {
+                        mbar_wait(&q_full[i], q_ld[i] & 1);
+                        tc_fence_after();
+                        q_seen[i] = true;
+                    }
+                };
+#ifdef MFA_Q_TOGETHER
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i)
-                    if (w.n_i[i] > 0) mbar_wait(&q_full[i], q_ld[i] & 1);
+                    if (w.n_i[i] > 0) await_q(i);
+#endif
                 if (n_max > 0) {
                     const int sK = it % kStages;
                     mbar_wait(&kv_full[sK], (it / kStages) & 1);
                     ++it;
                     tc_fence_after();
-                    MFA_TR(2, 0, 7);   // Q tiles and K(first) of the item landed
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i)
                         if (w.active(i, w.j_lo)) {
+                            await_q(i);
+                            if (i == 0) MFA_TR(2, 0, 7);   // Q tile 0 and K(first) of the item landed
                             issue_S(i, sK);
                             release_q(w, i, w.j_lo);
                         }
@@ -489,6 +524,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     }
                     tc_fence_after();
                     MFA_TR(2, j - w.j_lo, 0);
+                    if (!has_next && nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i) {
                         if (w.active(i, j)) {
@@ -505,6 +541,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                             issue_PV(i, sV, j > w.lo_i[i], kBN / 32, kBN / 16, true);
                         }
                         if (w.active(i, j + 1)) {
+                            await_q(i);
                             issue_S(i, sK);
                             release_q(w, i, j + 1);
                         }
@@ -513,6 +550,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     commit(&kv_empty[sV]);
                     if (has_next) commit(&kv_empty[sK]);
                 }
+                if (n_max <= w.j_lo && nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);   // (item without KV work)
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i) t_cnt[i] += (uint32_t)w.count(i);
 #ifdef MFA_TRACE
@@ -533,9 +571,14 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
         const uint32_t tO = tmem_base + lane_sel + Cfg::kTmemO + i * DPAD;
         const float c2 = p.scale_log2;
         uint32_t t_cnt = 0;   // KV tiles this warpgroup has processed so far (parity base)
+        PrefillItem w_next = prefill_item<kNQ>(p, blockIdx.x);   // (computed under the epilogue's wait for the last P.V, see the MMA warp)
         for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-            const PrefillItem w = prefill_item<kNQ>(p, item);
-            if (!w.valid) continue;
+            const PrefillItem w = w_next;
+            const int nxt = item + (int)gridDim.x;
+            if (!w.valid) {
+                if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+                continue;
+            }
 #ifdef MFA_TRACE
             tr_on = tr_cta;
 #endif
@@ -687,6 +730,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                           (p.cu_seqlens_q ? (int64_t)(w.q_off + qrow) * p.o_row_stride
                                           : (int64_t)w.b * p.o_batch_stride + (int64_t)qrow * p.o_row_stride);
                 MFA_TRI(3 + i, 0);
+                if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
                 if (n_mine > 0) {
                     mbar_wait(&o_full[i], (t_cnt + (uint32_t)n_mine - 1u) & 1u);
                     tc_fence_after();
@@ -697,6 +741,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 if (p.lse != nullptr && row_ok)   // natural-log LSE of the scaled scores (the reference drops it, api.cpp:436)
                     p.lse[(int64_t)w.b * p.lse_batch_stride + (int64_t)w.h * p.lse_head_stride + w.q_off + qrow] =
                         (l_row == 0.f || l_row != l_row) ? -INFINITY : (m_run * c2 + log2f(l_row)) * 0.6931471805599453f;
+#ifdef MFA_EPI_DIRECT
 #pragma unroll
                 for (int c = 0; c < DPAD / 32; ++c) {
                     uint32_t o[32];
@@ -721,6 +766,52 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                         }
                     }
                 }
+#else
+                // A thread holds a whole output row, but 32 lanes storing 16 bytes each to 32 different rows is the worst
+                // pattern for the memory pipe.  Each warp transposes its 32 rows through a private 4 KB staging area, 64
+                // columns (128 bytes per row) at a time, and stores whole 128-byte lines: 8 lanes per row, 4 rows per
+                // instruction.  16-byte pieces are XOR-swizzled by the row so that both phases are bank-conflict free; the
+                // area is private to the warp, so __syncwarp is all the synchronisation there is.
+                const uint32_t stage = smem_u32(smem + Cfg::kBarOffset + 512 + warp * Cfg::kOStageWarpBytes);
+                const int row0_w = m0 + i * kBM + (warp & 3) * 32;   // sequence row of lane 0
+                T* obase = static_cast<T*>(p.o) + (int64_t)w.h * p.o_head_stride +
+                           (p.cu_seqlens_q ? (int64_t)(w.q_off + row0_w) * p.o_row_stride
+                                           : (int64_t)w.b * p.o_batch_stride + (int64_t)row0_w * p.o_row_stride);
+#pragma unroll
+                for (int r = 0; r < DPAD / 64; ++r) {
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        uint32_t o[32];
+                        if (n_mine > 0) {   // warp-uniform
+                            tmem_ld32(tO + (2 * r + h2) * 32, o);
+                            tmem_wait_ld();
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 32; ++e) o[e] = 0u;
+                        }
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) {
+                            uint4 x;
+                            x.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
+                            x.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
+                            x.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
+                            x.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
+                            sts128(stage + lane * 128 + (((h2 * 4 + v) ^ (lane & 7)) * 16), x);
+                        }
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int pass = 0; pass < 8; ++pass) {
+                        const int row = pass * 4 + (lane >> 3);
+                        const int piece = lane & 7;
+                        const uint4 x = lds128(stage + row * 128 + ((piece ^ (row & 7)) * 16));
+                        const int col = r * 64 + piece * 8;
+                        if (row0_w + row < len_q && col < p.head_dim)
+                            *reinterpret_cast<uint4*>(obase + (int64_t)row * p.o_row_stride + col) = x;
+                    }
+                    __syncwarp();
+                }
+#endif
             }
             MFA_TRI(3 + i, 2);
             t_cnt += (uint32_t)n_mine;
