@@ -310,9 +310,9 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             // exited, or be re-armed before it landed).  q_full / q_empty phases therefore count LOADS of tile i
             // (q_ld[i]), not items: every load is awaited by the MMA warp before it commits q_empty, and the producer
             // observes that commit before the next load, so neither barrier ever runs more than one phase ahead.
-            // Order: Q tile 0, the item's first K tile, Q tile 1, the rest -- tile 0's buffer is free half a period before
-            // tile 1's (their chains interleave), and with its Q and K(first) in flight early tile 0 starts the item
-            // while tile 1 is still finishing the previous one.
+            // (Tried: Q tile 0, the item's first K tile, then Q tile 1 -- tile 0's buffer is free half a period before tile
+            // 1's -- with the MMA warp awaiting each Q tile in front of its own first S.  -DMFA_Q_SPLIT: S=256 +3 %, causal
+            // S=4096 / 1024 -3 %, everything else equal; the order stayed as it was.)
             auto load_q = [&](int i) {
                 if (w.n_i[i] == 0) return;
                 if (q_ld[i] > 0) mbar_wait(&q_empty[i], (q_ld[i] - 1) & 1);
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 ++q_ld[i];
             };
             load_q(0);
-#ifdef MFA_Q_TOGETHER   // A/B switch: the round-1 order (both Q tiles first, both awaited at the top of the item)
+#ifndef MFA_Q_SPLIT   // default: both Q tiles first (MFA_Q_SPLIT: Q tile 0, first K, Q tile 1 -- measured: causal -3 %, S=256 +3 %, else =)
             if constexpr (kNQ > 1) load_q(1);
 #endif
             MFA_TRI(3, 5);   // Q tile 0 issued
@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     __syncwarp();
                     if (j == w.j_lo && kv == 0) {
                         MFA_TRI(3, 6);   // first K load of the item issued
-#ifndef MFA_Q_TOGETHER
+#ifdef MFA_Q_SPLIT
                         if constexpr (kNQ > 1) load_q(1);
 #endif
                     }
@@ -478,9 +478,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 tr_on = tr_cta;
 #endif
                 const int n_max = w.n_max;
-                // Q tile i is awaited right in front of ITS first S MMA of the item, not at the top of the item: tile 0 of
-                // the next item starts as soon as its own Q (reloaded when tile 0's last S MMA finished, half a period
-                // before tile 1's) and the first K tile are there.
+                // (await_q(i) in front of tile i's first S MMA only matters under -DMFA_Q_SPLIT; by default both are awaited here)
                 bool q_seen[kNQ];
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i) q_seen[i] = false;
@@ -491,7 +489,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                         q_seen[i] = true;
                     }
                 };
-#ifdef MFA_Q_TOGETHER
+#ifndef MFA_Q_SPLIT
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i)
                     if (w.n_i[i] > 0) await_q(i);
@@ -524,7 +522,9 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     }
                     tc_fence_after();
                     MFA_TR(2, j - w.j_lo, 0);
+#ifndef MFA_NO_WNEXT
                     if (!has_next && nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+#endif
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i) {
                         if (w.active(i, j)) {
@@ -550,7 +550,11 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     commit(&kv_empty[sV]);
                     if (has_next) commit(&kv_empty[sK]);
                 }
+#ifndef MFA_NO_WNEXT
                 if (n_max <= w.j_lo && nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);   // (item without KV work)
+#else
+                if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+#endif
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i) t_cnt[i] += (uint32_t)w.count(i);
 #ifdef MFA_TRACE
@@ -730,7 +734,9 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                           (p.cu_seqlens_q ? (int64_t)(w.q_off + qrow) * p.o_row_stride
                                           : (int64_t)w.b * p.o_batch_stride + (int64_t)qrow * p.o_row_stride);
                 MFA_TRI(3 + i, 0);
+#ifndef MFA_NO_WNEXT
                 if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+#endif
                 if (n_mine > 0) {
                     mbar_wait(&o_full[i], (t_cnt + (uint32_t)n_mine - 1u) & 1u);
                     tc_fence_after();
@@ -742,78 +748,88 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     p.lse[(int64_t)w.b * p.lse_batch_stride + (int64_t)w.h * p.lse_head_stride + w.q_off + qrow] =
                         (l_row == 0.f || l_row != l_row) ? -INFINITY : (m_run * c2 + log2f(l_row)) * 0.6931471805599453f;
 #ifdef MFA_EPI_DIRECT
-#pragma unroll
-                for (int c = 0; c < DPAD / 32; ++c) {
-                    uint32_t o[32];
-                    if (n_mine > 0) {   // warp-uniform
-                        tmem_ld32(tO + c * 32, o);
-                        tmem_wait_ld();
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 32; ++e) o[e] = 0u;
-                    }
-                    if (row_ok) {
-#pragma unroll
-                        for (int v = 0; v < 4; ++v) {
-                            if (c * 32 + v * 8 < p.head_dim) {
-                                uint4 x;
-                                x.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
-                                x.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
-                                x.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
-                                x.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
-                                *reinterpret_cast<uint4*>(orow + c * 32 + v * 8) = x;
-                            }
-                        }
-                    }
-                }
+                constexpr bool kEpiDirect = true;
 #else
-                // A thread holds a whole output row, but 32 lanes storing 16 bytes each to 32 different rows is the worst
-                // pattern for the memory pipe.  Each warp transposes its 32 rows through a private 4 KB staging area, 64
-                // columns (128 bytes per row) at a time, and stores whole 128-byte lines: 8 lanes per row, 4 rows per
-                // instruction.  16-byte pieces are XOR-swizzled by the row so that both phases are bank-conflict free; the
-                // area is private to the warp, so __syncwarp is all the synchronisation there is.
-                const uint32_t stage = smem_u32(smem + Cfg::kBarOffset + 512 + warp * Cfg::kOStageWarpBytes);
-                const int row0_w = m0 + i * kBM + (warp & 3) * 32;   // sequence row of lane 0
-                T* obase = static_cast<T*>(p.o) + (int64_t)w.h * p.o_head_stride +
-                           (p.cu_seqlens_q ? (int64_t)(w.q_off + row0_w) * p.o_row_stride
-                                           : (int64_t)w.b * p.o_batch_stride + (int64_t)row0_w * p.o_row_stride);
+                constexpr bool kEpiDirect = false;
+#endif
+                // (Tried: direct stores for a Q tile that ends before its item does -- causal: tile 0 has one KV tile less than
+                // tile 1 -- to keep the staging traffic away from the other tile's last step: no gain, 542 vs 547 at S=1024.)
+                if (kEpiDirect) {
 #pragma unroll
-                for (int r = 0; r < DPAD / 64; ++r) {
-#pragma unroll
-                    for (int h2 = 0; h2 < 2; ++h2) {
+                    for (int c = 0; c < DPAD / 32; ++c) {
                         uint32_t o[32];
                         if (n_mine > 0) {   // warp-uniform
-                            tmem_ld32(tO + (2 * r + h2) * 32, o);
+                            tmem_ld32(tO + c * 32, o);
                             tmem_wait_ld();
                         } else {
 #pragma unroll
                             for (int e = 0; e < 32; ++e) o[e] = 0u;
                         }
+                        if (row_ok) {
 #pragma unroll
-                        for (int v = 0; v < 4; ++v) {
-                            uint4 x;
-                            x.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
-                            x.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
-                            x.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
-                            x.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
-                            sts128(stage + lane * 128 + (((h2 * 4 + v) ^ (lane & 7)) * 16), x);
+                            for (int v = 0; v < 4; ++v) {
+                                if (c * 32 + v * 8 < p.head_dim) {
+                                    uint4 x;
+                                    x.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
+                                    x.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
+                                    x.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
+                                    x.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
+                                    *reinterpret_cast<uint4*>(orow + c * 32 + v * 8) = x;
+                                }
+                            }
                         }
                     }
-                    __syncwarp();
+                } else {
+                    // A thread holds a whole output row, but 32 lanes storing 16 bytes each to 32 different rows is the worst
+                    // pattern for the memory pipe.  Each warp transposes its 32 rows through a private 4 KB staging area, 64
+                    // columns (128 bytes per row) at a time, and stores whole 128-byte lines: 8 lanes per row, 4 rows per
+                    // instruction.  16-byte pieces are XOR-swizzled by the row so that both phases are bank-conflict free; the
+                    // area is private to the warp, so __syncwarp is all the synchronisation there is.
+                    const uint32_t stage = smem_u32(smem + Cfg::kBarOffset + 512 + warp * Cfg::kOStageWarpBytes);
+                    const int row0_w = m0 + i * kBM + (warp & 3) * 32;   // sequence row of lane 0
+                    T* obase = static_cast<T*>(p.o) + (int64_t)w.h * p.o_head_stride +
+                               (p.cu_seqlens_q ? (int64_t)(w.q_off + row0_w) * p.o_row_stride
+                                               : (int64_t)w.b * p.o_batch_stride + (int64_t)row0_w * p.o_row_stride);
 #pragma unroll
-                    for (int pass = 0; pass < 8; ++pass) {
-                        const int row = pass * 4 + (lane >> 3);
-                        const int piece = lane & 7;
-                        const uint4 x = lds128(stage + row * 128 + ((piece ^ (row & 7)) * 16));
-                        const int col = r * 64 + piece * 8;
-                        if (row0_w + row < len_q && col < p.head_dim)
-                            *reinterpret_cast<uint4*>(obase + (int64_t)row * p.o_row_stride + col) = x;
+                    for (int r = 0; r < DPAD / 64; ++r) {
+#pragma unroll
+                        for (int h2 = 0; h2 < 2; ++h2) {
+                            uint32_t o[32];
+                            if (n_mine > 0) {   // warp-uniform
+                                tmem_ld32(tO + (2 * r + h2) * 32, o);
+                                tmem_wait_ld();
+                            } else {
+#pragma unroll
+                                for (int e = 0; e < 32; ++e) o[e] = 0u;
+                            }
+#pragma unroll
+                            for (int v = 0; v < 4; ++v) {
+                                uint4 x;
+                                x.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
+                                x.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
+                                x.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
+                                x.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
+                                sts128(stage + lane * 128 + (((h2 * 4 + v) ^ (lane & 7)) * 16), x);
+                            }
+                        }
+                        __syncwarp();
+#pragma unroll
+                        for (int pass = 0; pass < 8; ++pass) {
+                            const int row = pass * 4 + (lane >> 3);
+                            const int piece = lane & 7;
+                            const uint4 x = lds128(stage + row * 128 + ((piece ^ (row & 7)) * 16));
+                            const int col = r * 64 + piece * 8;
+                            if (row0_w + row < len_q && col < p.head_dim)
+                                *reinterpret_cast<uint4*>(obase + (int64_t)row * p.o_row_stride + col) = x;
+                        }
+                        __syncwarp();
                     }
-                    __syncwarp();
                 }
-#endif
             }
             MFA_TRI(3 + i, 2);
+#ifdef MFA_NO_WNEXT
+            if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+#endif
             t_cnt += (uint32_t)n_mine;
 #ifdef MFA_TRACE
             tr_base += n_mine;

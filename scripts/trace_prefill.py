@@ -49,6 +49,15 @@ if CAUSAL:
         for i in (0, 1):
             line += f"  WG{i} [{r(t[i, base[i], 0])}, {r(t[i, base[i], 1])}, {r(t[i, base[i] + n[i] - 1, 5])}, {r(ep[i, k, 1])}, {r(ep[i, k, 2])}]"
         print(line)
+        if mb == nmb - 1 and k > 0:
+            print("    steps of this item (relative to its MMA start): MMA [K/V ready, p_lo0, p_hi0, PV0+S0 issued, p_lo1, p_hi1, PV1+S1 issued] | WG0 [S ready, max done, P_lo, P_hi] | WG1 [...]")
+            z = int(t[2, mbase, 7])
+            rr = lambda x: int(x) - z if int(x) > 0 else -1
+            for j in range(n[1]):
+                l2 = f"      j={j} MMA {[rr(t[2, mbase + j, e]) for e in range(7)]}"
+                if j < n[0]: l2 += f" | WG0 {[rr(t[0, base[0] + j, e]) for e in (1, 6, 4, 5)]}"
+                l2 += f" | WG1 {[rr(t[1, base[1] + j, e]) for e in (1, 6, 4, 5)]}"
+                print(l2)
         base[0] += n[0]; base[1] += n[1]; mbase += n[1]; k += 1
     sys.exit(0)
 if S <= 2048:
