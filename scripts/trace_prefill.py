@@ -26,7 +26,6 @@ t0 = int(t[t > 0].min())
 r = lambda x: int(x) - t0 if int(x) > 0 else -1
 print("softmax events: 0 loop top, 1 S ready, 2 S in regs, 6 row max done, 7 grow vote done, 3 rescale done, 4 P_lo released, 5 P_hi released")
 print("mma events (single): 0 K/V ready, 1 p_lo0 seen, 2 p_hi0 seen, 3 PV0+S0 issued, 4 p_lo1 seen, 5 p_hi1 seen, 6 PV1+S1 issued")
-print("mma events (pair): 0 K(j+1) ready, 4 S(j+1) issued, 5 V(j) ready, 1 p_lo seen, 2 p_hi seen (PV lo issued), 3 PV hi issued")
 n = min(S // 128, 64)
 if CAUSAL:
     # causal: CTA 0 of a 147-CTA grid (coprime to the m-block count) runs items 0, 147, 294, ...; m-block = nmb-1 - item % nmb;
@@ -90,17 +89,3 @@ for role in (0, 1):
     seg = [[int(t[role, j, order[e + 1]] - t[role, j, order[e]]) for j in range(4, n - 1)] for e in range(len(order) - 1)]
     print("WG", role, "busy median", statistics.median(busy), "wait-for-S median", statistics.median(wait),
           "segments ld / max / vote / rescale / half0 / half1", [statistics.median(s) for s in seg])
-
-if int(pr[:, 0].max()) > 0:
-    print("producer (pair kernel): load index, what, t(before empty-wait), t(issued)")
-    print("   " + "  ".join(f"{i}:{'V' if int(pr[i,2])>=1000 else 'K'}{int(pr[i,2])%1000}@{r(pr[i,0])}/{r(pr[i,1])}" for i in range(24)))
-    print("   K loads: elect-block entry / after expect_tx / after TMA 1 / after TMA 2")
-    print("   " + "  ".join(f"{i}:{r(pr[i,3])}/{r(pr[i,4])}/{r(pr[i,5])}/{r(pr[i,6])}" for i in range(16) if int(pr[i,2]) < 1000))
-if int(ct[:, 0].max()) > 0:
-    print("CTA lifetime (pair kernel; CTAs (x,0,B/2)): cycles entry->setup, ->first S, ->loop end, ->epilogue end, ->exit; wall ns; MHz")
-    for x in range(0, 64):
-        if int(ct[x, 0]) == 0:
-            continue
-        c = [int(v) for v in ct[x]]
-        ns = c[7] - c[6]
-        print(f"  x={x:2d} setup {c[1]-c[0]:6d} firstS {c[2]-c[0]:6d} loop_end {c[3]-c[0]:7d} epi {c[4]-c[0]:7d} exit {c[5]-c[0]:7d}  wall {ns:7d} ns  {1000.0*(c[5]-c[0])/max(ns,1):6.0f} MHz  start@{c[6] - int(ct[:,6][ct[:,6]>0].min()):8d} ns")
