@@ -136,6 +136,21 @@ int    mfa_decode_num_splits(const mfa_params_t* p);
 size_t mfa_decode_workspace_bytes(const mfa_params_t* p, int num_splits);
 int    mfa_decode_fwd(const mfa_params_t* p, void* workspace, size_t workspace_bytes, void* cuda_stream);
 
+/* --- decode without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ *     callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ *     it).  Same arguments, result and errors as mfa_decode_fwd, but the split-KV scratch is a file-scope
+ *     `static __device__` array inside the library: MFA_DECODE_STATIC_WS_BYTES (8 MiB) of device memory on every GPU that
+ *     loads the library, held until the process exits.  The call performs no cudaMalloc / cudaFree and calls no allocating
+ *     library routine; inputs and outputs are still the caller's.  A problem whose scratch
+ *     (mfa_decode_workspace_bytes for the split count in use) exceeds the array is REJECTED with MFA_ERR_UNSUPPORTED and a
+ *     message naming both sizes -- pass a smaller p->num_splits, or use mfa_decode_fwd.  One split needs no scratch.
+ *     All calls on a device share the one array and it keeps the previous call's contents (nothing in it has to start at
+ *     zero: every partial is written before it is read).  Calls that OVERLAP on the GPU -- two streams, or two host
+ *     threads on one device -- race on it; calls on one stream are ordered and safe. */
+#define MFA_DECODE_STATIC_WS_BYTES (8u << 20)
+size_t mfa_decode_static_workspace_limit(void);
+int    mfa_decode_fwd_static(const mfa_params_t* p, void* cuda_stream);
+
 /* --- KV-cache append (the reference's docstring mentions it, interface.py:110-111, but does not
  *     implement it): write s_new new K/V rows per sequence into the cache IN PLACE at logical positions
  *     seqlens_k[b] .. seqlens_k[b] + s_new - 1 (paged through block_table, or contiguous), and -- when

@@ -67,7 +67,7 @@ class MfaAppendParams(ctypes.Structure):
 EXPORTS = (
     "mfa_abi_version", "mfa_last_error", "mfa_device_supported", "mfa_prefill_fwd", "mfa_decode_num_splits",
     "mfa_decode_workspace_bytes", "mfa_decode_fwd", "mfa_combine_partials", "mfa_launch_count", "mfa_selftest_umma",
-    "mfa_debug_set_trace", "mfa_selftest_umma2", "mfa_kvcache_append",
+    "mfa_debug_set_trace", "mfa_selftest_umma2", "mfa_kvcache_append", "mfa_decode_static_workspace_limit", "mfa_decode_fwd_static",
     "mfa_xchg_create", "mfa_xchg_export", "mfa_xchg_connect", "mfa_xchg_connect_ptrs", "mfa_xchg_local_ptr",
     "mfa_xchg_status", "mfa_xchg_clear_status", "mfa_xchg_destroy", "mfa_decode_kv_sharded_workspace_bytes", "mfa_decode_fwd_kv_sharded",
 )
@@ -102,6 +102,10 @@ def load() -> ctypes.CDLL:
     lib.mfa_decode_workspace_bytes.restype = ctypes.c_size_t
     lib.mfa_decode_fwd.argtypes = [P, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
     lib.mfa_decode_fwd.restype = ctypes.c_int
+    lib.mfa_decode_static_workspace_limit.argtypes = []
+    lib.mfa_decode_static_workspace_limit.restype = ctypes.c_size_t
+    lib.mfa_decode_fwd_static.argtypes = [P, ctypes.c_void_p]
+    lib.mfa_decode_fwd_static.restype = ctypes.c_int
     lib.mfa_combine_partials.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
                                          ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
     lib.mfa_combine_partials.restype = ctypes.c_int

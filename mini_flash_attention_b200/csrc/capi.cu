@@ -474,6 +474,48 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
     return MFA_OK;
 }
 
+// ------------------------------------------------------------------------------------------ decode without allocation
+// The split-KV scratch (fp32 partials + LSEs) of mfa_decode_fwd_static lives in the library image instead of a caller
+// buffer: MFA_DECODE_STATIC_WS_BYTES of device memory on every GPU that loads the library, held until exit.  The name
+// below is a device symbol; in HOST code it is only a stand-in, so the launch path gets the array's device address from
+// cudaGetSymbolAddress -- once per device, with that device current -- and passes that pointer on.
+static __device__ __align__(256) unsigned char g_decode_static_ws[MFA_DECODE_STATIC_WS_BYTES];
+
+static int decode_static_ws_ptr(void** out) {
+    static std::atomic<void*> ptr_of[64];   // per device; zero-initialised
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    if (dev < 0 || dev >= 64) return fail(MFA_ERR_UNSUPPORTED, "device ordinal %d beyond the 64 this entry point tracks", dev);
+    void* ptr = ptr_of[dev].load(std::memory_order_acquire);
+    if (!ptr) {
+        e = cudaGetSymbolAddress(&ptr, g_decode_static_ws);   // the address on the CURRENT device
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(decode scratch)");
+        if (!ptr) return fail(MFA_ERR_CUDA, "cudaGetSymbolAddress returned a null decode scratch address");
+        ptr_of[dev].store(ptr, std::memory_order_release);
+    }
+    *out = ptr;
+    return MFA_OK;
+}
+
+size_t mfa_decode_static_workspace_limit(void) { return (size_t)MFA_DECODE_STATIC_WS_BYTES; }
+
+int mfa_decode_fwd_static(const mfa_params_t* p, void* cuda_stream) {
+    int rc = check_common(p);
+    if (rc) return rc;
+    const int splits = decode_splits_for(p);
+    const size_t need = mfa_decode_workspace_bytes(p, splits);
+    if (need > (size_t)MFA_DECODE_STATIC_WS_BYTES)
+        return fail(MFA_ERR_UNSUPPORTED,
+                    "mfa_decode_fwd_static: %d splits x %d rows x head_dim %d need %zu bytes of scratch, the built-in array holds %zu; "
+                    "lower num_splits or call mfa_decode_fwd with a caller workspace",
+                    splits, p->batch * p->heads, p->head_dim, need, (size_t)MFA_DECODE_STATIC_WS_BYTES);
+    void* ws = nullptr;
+    if (need > 0 && (rc = decode_static_ws_ptr(&ws))) return rc;
+    // The partials are fully written by the split-KV kernel before the combine reads them: nothing has to start at zero.
+    return decode_impl(p, ws, need ? (size_t)MFA_DECODE_STATIC_WS_BYTES : 0, nullptr, cuda_stream);
+}
+
 // ------------------------------------------------------------------------------------------ KV-shard exchange
 int mfa_xchg_create(int world, int rank, int max_rows, int head_dim, mfa_xchg_t** out) {
     if (!out) return fail(MFA_ERR_INVALID_ARG, "null out");
