@@ -312,10 +312,11 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             // (q_ld[i]), not items: every load is awaited by the MMA warp before it commits q_empty, and the producer
             // observes that commit before the next load, so neither barrier ever runs more than one phase ahead.
             // (Tried: Q tile 0, the item's first K tile, then Q tile 1 -- tile 0's buffer is free half a period before tile
-            // 1's -- with the MMA warp awaiting each Q tile in front of its own first S.  -DMFA_Q_SPLIT: S=256 +3 %, causal
-            // S=4096 / 1024 -3 %, everything else equal; the order stayed as it was.)
-            auto load_q = [&](int i) {
-                if (w.n_i[i] == 0) return;
+            // 1's -- with the MMA warp awaiting each Q tile in front of its own first S: S=256 +3 %, causal -3 %; and the
+            // per-tile wait bookkeeping alone cost the MMA warp 8 % on the short causal shapes.  Removed.)
+#pragma unroll
+            for (int i = 0; i < kNQ; ++i) {
+                if (w.n_i[i] == 0) continue;
                 if (q_ld[i] > 0) mbar_wait(&q_empty[i], (q_ld[i] - 1) & 1);
                 if (elect_one()) {
                     mbar_arrive_expect_tx(&q_full[i], Cfg::kQTileBytes);
@@ -326,12 +327,8 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 }
                 __syncwarp();
                 ++q_ld[i];
-            };
-            load_q(0);
-#ifndef MFA_Q_SPLIT   // default: both Q tiles first (MFA_Q_SPLIT: Q tile 0, first K, Q tile 1 -- measured: causal -3 %, S=256 +3 %, else =)
-            if constexpr (kNQ > 1) load_q(1);
-#endif
-            MFA_TRI(3, 5);   // Q tile 0 issued
+            }
+            MFA_TRI(3, 5);   // Q loads issued
             const int32_t* bt = p.block_table ? p.block_table + (int64_t)w.b * p.block_table_batch_stride : nullptr;
             const bool packed_k = (p.cu_seqlens_k != nullptr) && (bt == nullptr);
             // rows >= len_k of a V tile must be zero (P is 0 there, but 0 * NaN = NaN).  For fixed-length
@@ -373,12 +370,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                         }
                     }
                     __syncwarp();
-                    if (j == w.j_lo && kv == 0) {
-                        MFA_TRI(3, 6);   // first K load of the item issued
-#ifdef MFA_Q_SPLIT
-                        if constexpr (kNQ > 1) load_q(1);
-#endif
-                    }
+                    if (j == w.j_lo && kv == 0) MFA_TRI(3, 6);   // first K load of the item issued
                     if (fix) {
                         // wait for the bytes, zero rows [rows_valid, 128) of every sub-tile, publish to the MMA proxy
                         mbar_wait(tail_bar, tail_phase);
@@ -479,22 +471,9 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                 tr_on = tr_cta;
 #endif
                 const int n_max = w.n_max;
-                // (await_q(i) in front of tile i's first S MMA only matters under -DMFA_Q_SPLIT; by default both are awaited here)
-                bool q_seen[kNQ];
-#pragma unroll
-                for (int i = 0; i < kNQ; ++i) q_seen[i] = false;
-                auto await_q = [&](int i) {
-                    if (!q_seen[i]) {
-                        mbar_wait(&q_full[i], q_ld[i] & 1);
-                        tc_fence_after();
-                        q_seen[i] = true;
-                    }
-                };
-#ifndef MFA_Q_SPLIT
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i)
-                    if (w.n_i[i] > 0) await_q(i);
-#endif
+                    if (w.n_i[i] > 0) mbar_wait(&q_full[i], q_ld[i] & 1);
                 if (n_max > 0) {
                     const int sK = it % kStages;
                     mbar_wait(&kv_full[sK], (it / kStages) & 1);
@@ -503,8 +482,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i)
                         if (w.active(i, w.j_lo)) {
-                            await_q(i);
-                            if (i == 0) MFA_TR(2, 0, 7);   // Q tile 0 and K(first) of the item landed
+                            if (i == 0) MFA_TR(2, 0, 7);   // Q tiles and K(first) of the item landed
                             issue_S(i, sK);
                             release_q(w, i, w.j_lo);
                         }
@@ -542,7 +520,6 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                             issue_PV(i, sV, j > w.lo_i[i], kBN / 32, kBN / 16, true);
                         }
                         if (w.active(i, j + 1)) {
-                            await_q(i);
                             issue_S(i, sK);
                             release_q(w, i, j + 1);
                         }
@@ -764,8 +741,10 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
 #else
                 constexpr bool kEpiDirect = false;
 #endif
-                // (Tried: direct stores for a Q tile that ends before its item does -- causal: tile 0 has one KV tile less than
-                // tile 1 -- to keep the staging traffic away from the other tile's last step: no gain, 542 vs 547 at S=1024.)
+                // (Tried and not kept: direct stores for a Q tile that ends before its item does -- causal: tile 0 has one KV tile
+                // less than tile 1 --, and the direct form chosen per launch for short causal problems: the compile-time
+                // direct build, -DMFA_EPI_DIRECT, is 1.5 % (S=1024) to 5 % (S=512) faster on those and 10-25 % slower on the
+                // short non-causal ones; with both forms in one kernel the gain shrinks to 1 %.)
                 if (kEpiDirect) {
 #pragma unroll
                     for (int c = 0; c < DPAD / 32; ++c) {
