@@ -20,12 +20,12 @@
 namespace mfa {
 cudaError_t launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeKParams& p, bool is_bf16,
                           int dpad, cudaStream_t stream);
-cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream, bool dependent);
+cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream);
 cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                            const PrefillKParams& p, bool is_bf16, int dpad, cudaStream_t stream);
 int prefill_rows_per_cta(int dpad);
 cudaError_t launch_kvcache_append(const mfa_append_params_t& p, int sm_count, cudaStream_t stream);
-cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream, bool dependent);
+cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream);
 }  // namespace mfa
 
 // Exchange buffer of the KV-sharded decode (include/mfa_b200.h; kernel in xchg_sm100.cu).  One cudaMalloc per rank:
@@ -420,8 +420,6 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
     kp.k_scale = fp8 ? p->k_scale_ptr : nullptr;
     kp.v_scale = fp8 ? p->v_scale_ptr : nullptr;
 
-    // the merge kernel behind a split launch is a programmatic dependent of it (MFA_DECODE_NO_PDL=1: plain stream order)
-    static const bool use_pdl = [] { const char* e = getenv("MFA_DECODE_NO_PDL"); return !(e && e[0] == '1'); }();
     cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
     cudaError_t e = mfa::launch_decode(tmK, tmV, kp, bf16, dpad, stream);
     if (e != cudaSuccess) return cuda_fail(e, "decode launch");
@@ -448,7 +446,7 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
         xp.max_rows = x->max_rows;
         xp.head_dim = D;
         xp.heads = p->heads;
-        e = mfa::launch_xchg_merge(xp, bf16, stream, use_pdl);
+        e = mfa::launch_xchg_merge(xp, bf16, stream);
         if (e != cudaSuccess) return cuda_fail(e, "exchange-merge launch");
         g_launches.fetch_add(1);
         return MFA_OK;
@@ -467,7 +465,7 @@ static int decode_impl(const mfa_params_t* p, void* workspace, size_t workspace_
         cp.rows = (int)rows;
         cp.head_dim = D;
         cp.packed = 0;
-        e = mfa::launch_combine(cp, bf16, stream, use_pdl);
+        e = mfa::launch_combine(cp, bf16, stream);
         if (e != cudaSuccess) return cuda_fail(e, "combine launch");
         g_launches.fetch_add(1);
     }
@@ -684,7 +682,7 @@ int mfa_combine_partials(const float* packed, int num_partials, int rows, int he
     cp.rows = rows;
     cp.head_dim = head_dim;
     cp.packed = 1;
-    cudaError_t e = mfa::launch_combine(cp, is_bf16 != 0, static_cast<cudaStream_t>(cuda_stream), false);
+    cudaError_t e = mfa::launch_combine(cp, is_bf16 != 0, static_cast<cudaStream_t>(cuda_stream));
     if (e != cudaSuccess) return cuda_fail(e, "combine launch");
     g_launches.fetch_add(1);
     return MFA_OK;

@@ -192,9 +192,6 @@ __global__ void MFA_DECODE_BOUNDS(DPAD) decode_splitkv_kernel(const __grid_const
         fence_barrier_init();
     }
     __syncthreads();
-    // The merge kernel behind a split launch (combine or exchange-merge) is a programmatic dependent: let it be scheduled
-    // now -- its CTAs fit next to ours and wait in griddepcontrol.wait until this grid has completed.
-    griddep_launch_dependents();
 
     if (warp == 4) {
         // ------------------------------------------------------------ TMA producer
@@ -536,7 +533,6 @@ __global__ void __launch_bounds__(kMergeThreads) combine_kernel(const __grid_con
     const int D = p.head_dim;
     float4 acc[2];
     float glse;
-    griddep_wait();   // (launched as a programmatic dependent of the split-KV kernel: its partials are complete from here on)
     block_merge_splits<kPacked>(p.o_part, p.lse_part, p.num_splits, p.rows, row, D, acc, glse, red);
     if (threadIdx.x >= 32) return;
     const int64_t out_off = (p.heads > 0) ? (int64_t)(row / p.heads) * p.out_batch_stride +
@@ -618,21 +614,20 @@ cudaError_t launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const 
 #undef MFA_DECODE_CASE
 }
 
-// `dependent`: launch as a programmatic dependent of the kernel in front of it in the stream (the split-KV kernel).
-cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream, bool dependent) {
-    void (*kern)(CombineKParams) = p.packed ? (is_bf16 ? combine_kernel<__nv_bfloat16, true> : combine_kernel<__half, true>)
-                                            : (is_bf16 ? combine_kernel<__nv_bfloat16, false> : combine_kernel<__half, false>);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(p.rows);
-    cfg.blockDim = dim3(kMergeThreads);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = dependent ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, kern, p);
+cudaError_t launch_combine(const CombineKParams& p, bool is_bf16, cudaStream_t stream) {
+    dim3 grid(p.rows);
+    if (p.packed) {
+        if (is_bf16)
+            combine_kernel<__nv_bfloat16, true><<<grid, kMergeThreads, 0, stream>>>(p);
+        else
+            combine_kernel<__half, true><<<grid, kMergeThreads, 0, stream>>>(p);
+    } else {
+        if (is_bf16)
+            combine_kernel<__nv_bfloat16, false><<<grid, kMergeThreads, 0, stream>>>(p);
+        else
+            combine_kernel<__half, false><<<grid, kMergeThreads, 0, stream>>>(p);
+    }
+    return cudaGetLastError();
 }
 
 }  // namespace mfa

@@ -283,12 +283,6 @@ __device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
     asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
     return d;
 }
-// Programmatic dependent launch (PDL): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
-// while its predecessor in the stream is still running; griddep_wait() blocks until that predecessor has completed and
-// its memory is visible (a no-op in a normal launch).  griddep_launch_dependents() in the predecessor lets the dependent
-// grid be scheduled early (its CTAs then sit in griddep_wait()), which takes the launch latency off the critical path.
-__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 // 16-byte shared-memory accesses by shared-window address (a generic pointer makes ptxas emit the slower generic ST / LD)
 __device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");

@@ -72,7 +72,6 @@ __global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_
     const int lane = threadIdx.x & 31;
     const int D = p.head_dim;
     const int DS = D + 4;   // row stride of the gather buffer: [O_0 .. O_{D-1}, LSE, pad x3] keeps rows 16-byte aligned
-    asm volatile("griddepcontrol.wait;" ::: "memory");   // programmatic dependent of this step's split-KV kernel (ptx.cuh: griddep_wait)
     // this step's epoch: launches completed so far + 1 (ctrs = {status, epoch counter, rows done})
     const uint32_t epoch = *reinterpret_cast<volatile const uint32_t*>(p.ctrs + 1) + 1u;
 
@@ -186,7 +185,7 @@ __global__ void __launch_bounds__(kMergeThreads) xchg_merge_kernel(const __grid_
 
 }  // namespace
 
-cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream, bool dependent) {
+cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t stream) {
     // The kernel spins until the peers arrive, so it must never stand in the way of the kernels it is waiting for.  An SM
     // re-partitions L1 / shared memory only when idle: a grid of these CTAs (8 KB static smem, small carve-out) on every
     // SM would block a split-KV kernel (100+ KB dynamic smem) of ANOTHER rank that shares the GPU (ranks as streams of
@@ -200,17 +199,12 @@ cudaError_t launch_xchg_merge(const XchgKParams& p, bool is_bf16, cudaStream_t s
         cudaFuncSetAttribute(xchg_merge_kernel<__half>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         attr_done[dev] = true;
     }
-    void (*kern)(XchgKParams) = is_bf16 ? xchg_merge_kernel<__nv_bfloat16> : xchg_merge_kernel<__half>;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(p.rows);
-    cfg.blockDim = dim3(kMergeThreads);
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = dependent ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, kern, p);
+    dim3 grid(p.rows);
+    if (is_bf16)
+        xchg_merge_kernel<__nv_bfloat16><<<grid, kMergeThreads, 0, stream>>>(p);
+    else
+        xchg_merge_kernel<__half><<<grid, kMergeThreads, 0, stream>>>(p);
+    return cudaGetLastError();
 }
 
 }  // namespace mfa

@@ -14,7 +14,6 @@ KVS = (512, 1024, 2048, 4096, 8192)
 shapes = ((24, 32, 8, KVS), (24, 24, 24, KVS)) if quick else ((24, 32, 8, KVS), (24, 24, 24, KVS), (8, 32, 8, KVS), (4, 64, 8, KVS))
 if small:   # the shapes that split: few (batch x KV head) items
     shapes = ((8, 32, 8, (2048, 8192)), (4, 64, 8, (2048, 8192)), (1, 32, 8, (16384, 65536, 131072)))
-print("mode:", "plain stream order" if os.environ.get("MFA_DECODE_NO_PDL") == "1" else "combine launched as a programmatic dependent")
 for B, Hq, Hkv, kvs in shapes:
     for KV in kvs:
         D, page = 128, 256
