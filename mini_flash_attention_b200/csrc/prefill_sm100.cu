@@ -781,39 +781,45 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     T* obase = static_cast<T*>(p.o) + (int64_t)w.h * p.o_head_stride +
                                (p.cu_seqlens_q ? (int64_t)(w.q_off + row0_w) * p.o_row_stride
                                                : (int64_t)w.b * p.o_batch_stride + (int64_t)row0_w * p.o_row_stride);
+                    // The O row is read from TMEM in groups of up to 128 columns with ONE wait per group (the S registers are
+                    // free here): four dependent load -> wait round trips per row were ~600 cycles of every item boundary.
+                    constexpr int kGroup = (DPAD >= 128) ? 128 : DPAD;
 #pragma unroll
-                    for (int r = 0; r < DPAD / 64; ++r) {
+                    for (int g0 = 0; g0 < DPAD; g0 += kGroup) {
+                        uint32_t o[kGroup];
+                        if (n_mine > 0) {   // warp-uniform
 #pragma unroll
-                        for (int h2 = 0; h2 < 2; ++h2) {
-                            uint32_t o[32];
-                            if (n_mine > 0) {   // warp-uniform
-                                tmem_ld32(tO + (2 * r + h2) * 32, o);
-                                tmem_wait_ld();
-                            } else {
+                            for (int c = 0; c < kGroup / 32; ++c)
+                                tmem_ld32(tO + g0 + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&o[c * 32]));
+                            tmem_wait_ld();
+                        } else {
 #pragma unroll
-                                for (int e = 0; e < 32; ++e) o[e] = 0u;
-                            }
+                            for (int e = 0; e < kGroup; ++e) o[e] = 0u;
+                        }
 #pragma unroll
-                            for (int v = 0; v < 4; ++v) {
+                        for (int r = 0; r < kGroup / 64; ++r) {
+#pragma unroll
+                            for (int v = 0; v < 8; ++v) {
+                                const uint32_t* ov = &o[r * 64 + v * 8];
                                 uint4 x;
-                                x.x = Elem<T>::pack(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
-                                x.y = Elem<T>::pack(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
-                                x.z = Elem<T>::pack(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
-                                x.w = Elem<T>::pack(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
-                                sts128(stage + lane * 128 + (((h2 * 4 + v) ^ (lane & 7)) * 16), x);
+                                x.x = Elem<T>::pack(__uint_as_float(ov[0]) * inv, __uint_as_float(ov[1]) * inv);
+                                x.y = Elem<T>::pack(__uint_as_float(ov[2]) * inv, __uint_as_float(ov[3]) * inv);
+                                x.z = Elem<T>::pack(__uint_as_float(ov[4]) * inv, __uint_as_float(ov[5]) * inv);
+                                x.w = Elem<T>::pack(__uint_as_float(ov[6]) * inv, __uint_as_float(ov[7]) * inv);
+                                sts128(stage + lane * 128 + ((v ^ (lane & 7)) * 16), x);
                             }
-                        }
-                        __syncwarp();
+                            __syncwarp();
 #pragma unroll
-                        for (int pass = 0; pass < 8; ++pass) {
-                            const int row = pass * 4 + (lane >> 3);
-                            const int piece = lane & 7;
-                            const uint4 x = lds128(stage + row * 128 + ((piece ^ (row & 7)) * 16));
-                            const int col = r * 64 + piece * 8;
-                            if (row0_w + row < len_q && col < p.head_dim)
-                                *reinterpret_cast<uint4*>(obase + (int64_t)row * p.o_row_stride + col) = x;
+                            for (int pass = 0; pass < 8; ++pass) {
+                                const int row = pass * 4 + (lane >> 3);
+                                const int piece = lane & 7;
+                                const uint4 x = lds128(stage + row * 128 + ((piece ^ (row & 7)) * 16));
+                                const int col = g0 + r * 64 + piece * 8;
+                                if (row0_w + row < len_q && col < p.head_dim)
+                                    *reinterpret_cast<uint4*>(obase + (int64_t)row * p.o_row_stride + col) = x;
+                            }
+                            __syncwarp();
                         }
-                        __syncwarp();
                     }
                 }
             }
