@@ -133,3 +133,24 @@ def test_c_abi_rejects_bad_arguments_without_a_gpu(mfa_lib):
     P.num_splits = 1000
     assert mfa_lib.mfa_decode_num_splits(ctypes.byref(P)) == 128  # clamp to ceil(8192/64), api.cpp:325-327
     assert mfa_lib.mfa_decode_workspace_bytes(ctypes.byref(P), 4) == 4 * 8 * 65 * 4
+
+
+@pytest.mark.parametrize("B,H,Hkv,KV,want", [
+    (24, 32, 8, 512, 1), (24, 32, 8, 2048, 1), (24, 32, 8, 4096, 1),    # 192 items: unsplit ...
+    (24, 32, 8, 8192, 3),                                                # ... except long items cut into two full waves
+    (24, 24, 24, 8192, 1),                                               # 576 items: already two waves
+    (8, 32, 8, 1024, 2), (8, 32, 8, 4096, 4), (8, 32, 8, 8192, 4),      # one wave: slots / items
+    (4, 64, 8, 8192, 9),
+    (1, 32, 8, 65536, 37), (1, 32, 8, 1 << 20, 37),                     # long context: 296 slots / 8 KV heads
+    (1, 32, 8, 256, 1),                                                  # fewer than 8 tiles per split: no split
+])
+def test_decode_split_heuristic(mfa_lib, B, H, Hkv, KV, want):
+    """The split count fitted on the L2-cold sweep (scripts/decode_splits_gqa.py): splits =
+    min(slots / items, tiles / 8) with slots = 2 x 148.  Runs without a GPU (the SM count falls back to a B200's 148)."""
+    from mini_flash_attention_b200._lib import MfaParams
+    P = MfaParams()
+    P.q_ptr = P.k_ptr = P.v_ptr = P.o_ptr = 16
+    P.head_dim, P.heads, P.kv_heads, P.batch, P.seqlen_q, P.seqlen_k, P.num_splits = 128, H, Hkv, B, 1, KV, 0
+    if torch.cuda.is_available() and torch.cuda.get_device_properties(0).multi_processor_count != 148:
+        pytest.skip("fitted for 148 SMs")
+    assert mfa_lib.mfa_decode_num_splits(ctypes.byref(P)) == want
