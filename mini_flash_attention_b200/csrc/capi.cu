@@ -94,6 +94,10 @@ int check_device() {
 }
 
 int dpad_of(int d) { return d <= 64 ? 64 : (d <= 128 ? 128 : 256); }
+int prefill_dpad_of(int d) {   // (the decode kernel has no 192 form)
+    static const bool no192 = [] { const char* e = getenv("MFA_PREFILL_NO_D192"); return e && e[0] == '1'; }();   // A/B: pad 136..192 to 256 as before
+    return d <= 64 ? 64 : (d <= 128 ? 128 : ((d <= 192 && !no192) ? 192 : 256));
+}
 
 // checks shared by every entry point (api.cpp:126-153)
 int check_common(const mfa_params_t* p) {
@@ -147,7 +151,7 @@ int mfa_prefill_fwd(const mfa_params_t* p, void* cuda_stream) {
     if (reinterpret_cast<uintptr_t>(p->q_ptr) & 15) return fail(MFA_ERR_UNSUPPORTED, "q must be 16-byte aligned");
 
     const int D = p->head_dim;
-    const int dpad = dpad_of(D);
+    const int dpad = prefill_dpad_of(D);
     const bool bf16 = p->is_bf16 != 0;
 
     const bool window = p->local_window && (p->window_size_left >= 0 || p->window_size_right >= 0);

@@ -90,7 +90,7 @@ template <int DPAD>
 struct PrefillCfg {
     static constexpr int kBM = kPrefillBlockM;
     static constexpr int kBN = kPrefillBlockN;
-    static constexpr int kNQ = (DPAD <= 128) ? 2 : 1;            // Q tiles per CTA (TMEM budget)
+    static constexpr int kNQ = (DPAD <= 128) ? 2 : 1;            // Q tiles per CTA (TMEM budget: 128 S + DPAD O columns per tile of 512)
     static constexpr int kSoftmaxWarps = kNQ * 4;                // one thread per query row
     static constexpr int kThreads = (kSoftmaxWarps + 4) * 32;    // + one warpgroup {TMA warp, MMA warp, TMEM warp, spare}
     static constexpr int kSub = DPAD / 64;                       // 64-column (128-byte) sub-tiles per row
@@ -100,7 +100,7 @@ struct PrefillCfg {
 #ifndef MFA_STAGES128
 #define MFA_STAGES128 4
 #endif
-    static constexpr int kStages = (DPAD == 64) ? 8 : (DPAD == 128 ? MFA_STAGES128 : 2);
+    static constexpr int kStages = (DPAD == 64) ? 8 : (DPAD == 128 ? MFA_STAGES128 : (DPAD == 192 ? 3 : 2));
     static constexpr int kQBytes = kNQ * kQTileBytes;
     static constexpr int kRingBytes = kStages * kKVTileBytes;
     static constexpr int kBarOffset = kQBytes + kRingBytes;
@@ -783,7 +783,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                                                : (int64_t)w.b * p.o_batch_stride + (int64_t)row0_w * p.o_row_stride);
                     // The O row is read from TMEM in groups of up to 128 columns with ONE wait per group (the S registers are
                     // free here): four dependent load -> wait round trips per row were ~600 cycles of every item boundary.
-                    constexpr int kGroup = (DPAD >= 128) ? 128 : DPAD;
+                    constexpr int kGroup = (DPAD % 128 == 0) ? 128 : 64;
 #pragma unroll
                     for (int g0 = 0; g0 < DPAD; g0 += kGroup) {
                         uint32_t o[kGroup];
@@ -900,6 +900,7 @@ cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const
     switch (dpad) {
         MFA_PREFILL_CASE(64)
         MFA_PREFILL_CASE(128)
+        MFA_PREFILL_CASE(192)   // head_dim 136 ... 192: one Q tile per CTA like 256, but 3 instead of 4 sub-tiles of every operand
         MFA_PREFILL_CASE(256)
         default:
             return cudaErrorInvalidValue;

@@ -78,6 +78,16 @@ def test_other_head_dims(mfa, D, dt):  # the reference is wrong for 96/160/224 (
     _check(mfa, *_qkv(1, 130, 130, 2, 2, D, dtype=dt), True)
 
 
+@pytest.mark.parametrize("D", [136, 160, 192])
+@pytest.mark.parametrize("causal", [False, True])
+@DTYPES
+def test_head_dim_192_instantiation(mfa, D, causal, dt):
+    """head_dim 136 ... 192 runs the DPAD = 192 form of the kernel (one Q tile per CTA, 3 sub-tiles per operand): many KV
+    tiles, a ragged last tile, GQA, and more work items than CTAs (the persistent multi-item path)."""
+    _check(mfa, *_qkv(1, 777, 777, 8, 2, D, seed=5, dtype=dt), causal)
+    _check(mfa, *_qkv(4, 1024, 1024, 16, 4, D, seed=6, dtype=dt), causal)   # 4 x 16 x 8 = 512 items
+
+
 @pytest.mark.parametrize("B", [1, 2, 4, 8])
 @DTYPES
 def test_batch_sizes(mfa, B, dt):  # test_mha.py:109
