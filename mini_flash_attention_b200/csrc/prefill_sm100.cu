@@ -242,6 +242,16 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int total_items = p.num_m_blocks * p.heads * p.batch;
+    // Item walk of a persistent CTA: round k hands out items k * grid ... k * grid + grid - 1.  Packed (ragged) batches are
+    // listed by descending cost, so odd rounds run backwards (p.snake): the CTA that drew the heaviest item of one round gets
+    // the lightest of the next, which bounds the imbalance by the cost drop inside ONE round instead of the whole list.
+    const int n_rounds = (total_items + (int)gridDim.x - 1) / (int)gridDim.x;
+    auto item_at = [&](int k) -> int {   // total_items = this CTA has no item in round k
+        if (k >= n_rounds) return total_items;
+        const int pos = (p.snake && (k & 1)) ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
+        const int it = k * (int)gridDim.x + pos;
+        return it < total_items ? it : total_items;
+    };
     constexpr int kWarpTma = Cfg::kSoftmaxWarps, kWarpMma = kWarpTma + 1, kWarpTmem = kWarpTma + 2;
 #ifdef MFA_TRACE
     const bool tr_cta = p.trace && blockIdx.x == 0 && lane == 0 && (warp == kWarpMma || warp == kWarpTma || (warp < kWarpTma && (warp & 3) == 0));
@@ -297,7 +307,9 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
         uint32_t tail_phase = 0;
         int it = 0;                  // K/V ring position, runs across items
         uint32_t q_ld[2] = {0, 0};   // loads of Q tile i so far (parity base of q_full / q_empty)
-        for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        for (int k = 0; k < n_rounds; ++k) {
+            const int item = item_at(k);
+            if (item >= total_items) continue;
             const PrefillItem w = prefill_item<kNQ>(p, item);
             if (!w.valid) continue;
             const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
@@ -460,9 +472,11 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             // The descriptor of the NEXT item (a handful of integer divisions, ~1000 cycles of dependent latency for a lone
             // warp) is computed while this warp waits for the last P of the current one, not between the items.
             PrefillItem w_next = prefill_item<kNQ>(p, blockIdx.x);
-            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+            for (int k = 0; k < n_rounds; ++k) {
+                const int item = item_at(k);
+                if (item >= total_items) continue;
                 const PrefillItem w = w_next;
-                const int nxt = item + (int)gridDim.x;
+                const int nxt = item_at(k + 1);
                 if (!w.valid) {
                     if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
                     continue;
@@ -554,9 +568,11 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
         const float c2 = p.scale_log2;
         uint32_t t_cnt = 0;   // KV tiles this warpgroup has processed so far (parity base)
         PrefillItem w_next = prefill_item<kNQ>(p, blockIdx.x);   // (computed under the epilogue's wait for the last P.V, see the MMA warp)
-        for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        for (int k = 0; k < n_rounds; ++k) {
+            const int item = item_at(k);
+            if (item >= total_items) continue;
             const PrefillItem w = w_next;
-            const int nxt = item + (int)gridDim.x;
+            const int nxt = item_at(k + 1);
             if (!w.valid) {
                 if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
                 continue;
@@ -877,7 +893,7 @@ static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& t
     if (items <= 0 || items > 0x7fffffffLL) return cudaErrorInvalidValue;
     const int sms = (dev < 64 && sm_count[dev] > 0) ? sm_count[dev] : 148;
     long long ctas = items;
-    if (!non_persistent && p.cu_seqlens_q == nullptr && items > sms) {
+    if (!non_persistent && (p.cu_seqlens_q == nullptr || p.snake) && items > sms) {
         ctas = sms;
         if (p.has_hi) {
             auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };

@@ -191,3 +191,33 @@ def test_against_reference_golden(mfa):
         out = mfa.flash_attn_varlen_func(q, k, v, cu_q, cu_k, mq, mk, causal=bool(z["causal"]), block_table=bt)
         ref = torch.from_numpy(z["out"]).float().cuda()
         assert (out.float() - ref).abs().max().item() <= 2 * TOL["fp16"], name
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_packed_uniform_batch_runs_persistent(mfa, causal, dtype):
+    """A packed batch whose sequences (nearly) all have the maximum length runs with persistent CTAs in snake order
+    (capi.cu: fill ratio >= 0.9), here 768 items on <= 148 CTAs with a partial last round.  Same inputs through the
+    fixed-length entry point must give the same bits (same per-item arithmetic), and both must match the oracle."""
+    from oracle import ref_attention as R
+    B, S, H, Hkv, D = 6, 1024, 32, 8, 128
+    g = torch.Generator(device="cuda").manual_seed(11)
+    q = torch.randn(B, S, H, D, device="cuda", dtype=dtype, generator=g)
+    k = torch.randn(B, S, Hkv, D, device="cuda", dtype=dtype, generator=g)
+    v = torch.randn(B, S, Hkv, D, device="cuda", dtype=dtype, generator=g)
+    cu = _cu([S] * B)
+    out = mfa.flash_attn_varlen_func(q.reshape(B * S, H, D), k.reshape(B * S, Hkv, D), v.reshape(B * S, Hkv, D), cu, cu, S, S, causal=causal)
+    fixed = mfa.flash_attn_func(q, k, v, causal=causal)
+    assert torch.equal(out.reshape(B, S, H, D), fixed)
+    ref = R.attention_ref(q, k, v, causal)
+    assert (out.reshape(B, S, H, D).float() - ref).abs().max().item() <= TOL["fp16" if dtype == torch.float16 else "bf16"]
+    # nearly uniform (fill ratio 0.94): still persistent, one sequence shorter and not a multiple of the tile
+    lens = [S] * (B - 1) + [S - 370]
+    qs = torch.cat([q[b, :lens[b]] for b in range(B)]); ks = torch.cat([k[b, :lens[b]] for b in range(B)]); vs = torch.cat([v[b, :lens[b]] for b in range(B)])
+    cu2 = _cu(lens)
+    out2 = mfa.flash_attn_varlen_func(qs, ks, vs, cu2, cu2, S, S, causal=causal)
+    off = 0
+    for b in range(B):
+        r = R.attention_ref(q[b:b + 1, :lens[b]], k[b:b + 1, :lens[b]], v[b:b + 1, :lens[b]], causal)[0]
+        assert (out2[off:off + lens[b]].float() - r).abs().max().item() <= TOL["fp16" if dtype == torch.float16 else "bf16"]
+        off += lens[b]
