@@ -96,6 +96,7 @@ struct PrefillKParams {
     float* lse;                    // optional natural-log LSE: (B, H, Sq) fixed / (H, total_q) packed; -inf for empty rows
     int64_t lse_batch_stride, lse_head_stride;   // elements; the row index is q_off + row (q_off = 0 when fixed)
     int32_t snake;                 // packed batches run persistent with odd rounds of the item walk reversed (prefill_sm100.cu)
+    int32_t compact;               // ragged causal packed batch: the item list is the device-built table of the items that exist
     long long* trace;              // MFA_TRACE builds only: clock64() stamps of CTA (0,0,0), [role][iter][8]
 };
 

@@ -105,7 +105,11 @@ struct PrefillCfg {
     static constexpr int kRingBytes = kStages * kKVTileBytes;
     static constexpr int kBarOffset = kQBytes + kRingBytes;
     static constexpr int kOStageWarpBytes = 32 * 128;            // epilogue: 32 rows x 64 columns of 16-bit output per softmax warp
-    static constexpr int kSmemBytes = kBarOffset + 512 + kSoftmaxWarps * kOStageWarpBytes + 1024;   // barriers, output staging, alignment slack
+    // item table of a ragged packed batch (p.compact): int len_q[kSchedMaxBatch], int cum[kSchedMaxMBlocks + 1]
+    static constexpr int kSchedMaxBatch = 64, kSchedMaxMBlocks = 255;
+    static constexpr int kSchedOffset = kBarOffset + 512 + kSoftmaxWarps * kOStageWarpBytes;
+    static constexpr int kSchedBytes = (kSchedMaxBatch + kSchedMaxMBlocks + 1) * 4;
+    static constexpr int kSmemBytes = kSchedOffset + kSchedBytes + 1024;   // barriers, output staging, item table, alignment slack
     static constexpr uint32_t kTmemCols = 512;
     static constexpr uint32_t kTmemS = 0;                        // S_i at kTmemS + i*128
     static constexpr uint32_t kTmemO = 256;                      // O_i at kTmemO + i*DPAD
@@ -147,11 +151,36 @@ struct PrefillItem {
     __device__ __forceinline__ int count(int i) const { return n_i[i] - lo_i[i]; }
 };
 
-template <int kNQ>
-__device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int item) {
+// `sched` (p.compact only): shared-memory table {len_q[64], cum[num_m_blocks + 1]} built at kernel start, where cum[i] is
+// the number of (m-block, sequence) pairs that exist among the TOP i m-blocks.  `item` is then a position in the list of
+// the items that exist, ordered by descending m-block (= descending cost under the causal mask), then sequence, then head.
+template <int kNQ, bool kCompact>
+__device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int item, const int* sched) {
     PrefillItem w;
     int mraw, rest, mblk;
-    if (p.cu_seqlens_q) {
+    if constexpr (kCompact) {
+        const int* slen = sched;
+        const int* cum = sched + 64;
+        const int M = p.num_m_blocks;
+        const int pair = item / p.heads;            // which (m-block, sequence) pair
+        const int h = item - pair * p.heads;
+        int lo = 0, hi = M;                          // largest i with cum[i] <= pair
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (cum[mid] <= pair) lo = mid; else hi = mid;
+        }
+        mblk = M - 1 - lo;
+        int r = pair - cum[lo];                      // the r-th sequence that has this m-block
+        const int need = mblk * (kNQ * kPrefillBlockM);
+        int b = 0;
+        for (; b < p.batch - 1; ++b) {
+            if (slen[b] > need) {
+                if (r == 0) break;
+                --r;
+            }
+        }
+        rest = b * p.heads + h;
+    } else if (p.cu_seqlens_q) {
         // Packed (ragged) batches launch one CTA per item and the hardware hands them out in blockIdx order: the m-block
         // index is the SLOWEST digit and runs downwards, so the items that exist only in the long sequences -- under the
         // causal mask also the heaviest ones -- start first and the short tail items fill the gaps at the end
@@ -214,7 +243,10 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
 // tiles are still in the softmax, and the epilogue of item n overlaps the first S MMAs of item n+1.  (Measured before:
 // ~7 k cycles from CTA start to the first S and ~3 k of epilogue per ~115 k-cycle item at S=4096, 22 % at S=1024.)
 // All mbarrier parities therefore come from RUNNING counters: items done (q_full / q_empty) and tiles done per Q tile.
-template <typename T, int DPAD>
+// kCompact: a separate instantiation for ragged causal packed batches (p.compact) -- the item decode of that form costs
+// the MMA-issuing warp registers and instructions, and the fixed-length kernel is sensitive to both (measured: with the
+// branch at run time the headline lost 3 %, causal 7 %).
+template <typename T, int DPAD, bool kCompact>
 __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
     prefill_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const __grid_constant__ PrefillKParams p) {
@@ -241,17 +273,31 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int total_items = p.num_m_blocks * p.heads * p.batch;
-    // Item walk of a persistent CTA: round k hands out items k * grid ... k * grid + grid - 1.  Packed (ragged) batches are
-    // listed by descending cost, so odd rounds run backwards (p.snake): the CTA that drew the heaviest item of one round gets
-    // the lightest of the next, which bounds the imbalance by the cost drop inside ONE round instead of the whole list.
-    const int n_rounds = (total_items + (int)gridDim.x - 1) / (int)gridDim.x;
-    auto item_at = [&](int k) -> int {   // total_items = this CTA has no item in round k
-        if (k >= n_rounds) return total_items;
-        const int pos = (p.snake && (k & 1)) ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
-        const int it = k * (int)gridDim.x + pos;
-        return it < total_items ? it : total_items;
-    };
+    const int* sched = reinterpret_cast<const int*>(smem + Cfg::kSchedOffset);
+    if (kCompact && warp == 1) {
+        // Ragged packed batch: build the table of the items that exist (see prefill_item).  One warp, before the set-up
+        // barrier below; every role then derives the same item list from it.
+        int* slen = reinterpret_cast<int*>(smem + Cfg::kSchedOffset);
+        int* cum = slen + 64;
+        for (int b = lane; b < 64; b += 32) slen[b] = (b < p.batch) ? (p.cu_seqlens_q[b + 1] - p.cu_seqlens_q[b]) : 0;
+        __syncwarp();
+        const int M = p.num_m_blocks;
+        for (int i = lane; i < M; i += 32) {   // i-th m-block from the top
+            const int need = (M - 1 - i) * (kNQ * kPrefillBlockM);
+            int c = 0;
+            for (int b = 0; b < p.batch; ++b) c += (slen[b] > need) ? 1 : 0;
+            cum[i + 1] = c;
+        }
+        __syncwarp();
+        if (lane == 0) {
+            int a = 0;
+            cum[0] = 0;
+            for (int i = 0; i < M; ++i) {
+                a += cum[i + 1];
+                cum[i + 1] = a;
+            }
+        }
+    }
     constexpr int kWarpTma = Cfg::kSoftmaxWarps, kWarpMma = kWarpTma + 1, kWarpTmem = kWarpTma + 2;
 #ifdef MFA_TRACE
     const bool tr_cta = p.trace && blockIdx.x == 0 && lane == 0 && (warp == kWarpMma || warp == kWarpTma || (warp < kWarpTma && (warp & 3) == 0));
@@ -288,6 +334,18 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
     // every TMEM address below is a compile-time constant (no register, no address arithmetic in the 72-register MMA
     // warp).  Checked, not assumed.
     if (*tmem_slot != 0u) __trap();
+    // (after the set-up barrier: a ragged packed batch counts its items in the table warp 1 just built)
+    const int total_items = kCompact ? sched[64 + p.num_m_blocks] * p.heads : p.num_m_blocks * p.heads * p.batch;
+    // Item walk of a persistent CTA: round k hands out items k * grid ... k * grid + grid - 1.  Packed (ragged) batches are
+    // listed by descending cost, so odd rounds run backwards (p.snake): the CTA that drew the heaviest item of one round gets
+    // the lightest of the next, which bounds the imbalance by the cost drop inside ONE round instead of the whole list.
+    const int n_rounds = (total_items + (int)gridDim.x - 1) / (int)gridDim.x;
+    auto item_at = [&](int k) -> int {   // total_items = this CTA has no item in round k
+        if (k >= n_rounds) return total_items;
+        const int pos = (p.snake && (k & 1)) ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
+        const int it = k * (int)gridDim.x + pos;
+        return it < total_items ? it : total_items;
+    };
     constexpr uint32_t tmem_base = 0u;
 
     // Register re-balancing: the launch gives every thread 168 registers (65536 / 384 threads); the
@@ -310,7 +368,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
         for (int k = 0; k < n_rounds; ++k) {
             const int item = item_at(k);
             if (item >= total_items) continue;
-            const PrefillItem w = prefill_item<kNQ>(p, item);
+            const PrefillItem w = prefill_item<kNQ, kCompact>(p, item, sched);
             if (!w.valid) continue;
             const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
             const int q_b_coord = p.cu_seqlens_q ? 0 : w.b;
@@ -471,14 +529,14 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
             // The descriptor of the NEXT item (a handful of integer divisions, ~1000 cycles of dependent latency for a lone
             // warp) is computed while this warp waits for the last P of the current one, not between the items.
-            PrefillItem w_next = prefill_item<kNQ>(p, blockIdx.x);
+            PrefillItem w_next = prefill_item<kNQ, kCompact>(p, item_at(0), sched);
             for (int k = 0; k < n_rounds; ++k) {
                 const int item = item_at(k);
                 if (item >= total_items) continue;
                 const PrefillItem w = w_next;
                 const int nxt = item_at(k + 1);
                 if (!w.valid) {
-                    if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+                    if (nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);
                     continue;
                 }
 #ifdef MFA_TRACE
@@ -516,7 +574,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     tc_fence_after();
                     MFA_TR(2, j - w.j_lo, 0);
 #ifndef MFA_NO_WNEXT
-                    if (!has_next && nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+                    if (!has_next && nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);
 #endif
 #pragma unroll
                     for (int i = 0; i < kNQ; ++i) {
@@ -543,9 +601,9 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                     if (has_next) commit(&kv_empty[sK]);
                 }
 #ifndef MFA_NO_WNEXT
-                if (n_max <= w.j_lo && nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);   // (item without KV work)
+                if (n_max <= w.j_lo && nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);   // (item without KV work)
 #else
-                if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+                if (nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);
 #endif
 #pragma unroll
                 for (int i = 0; i < kNQ; ++i) t_cnt[i] += (uint32_t)w.count(i);
@@ -567,14 +625,14 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
         const uint32_t tO = tmem_base + lane_sel + Cfg::kTmemO + i * DPAD;
         const float c2 = p.scale_log2;
         uint32_t t_cnt = 0;   // KV tiles this warpgroup has processed so far (parity base)
-        PrefillItem w_next = prefill_item<kNQ>(p, blockIdx.x);   // (computed under the epilogue's wait for the last P.V, see the MMA warp)
+        PrefillItem w_next = prefill_item<kNQ, kCompact>(p, item_at(0), sched);   // (computed under the epilogue's wait for the last P.V, see the MMA warp)
         for (int k = 0; k < n_rounds; ++k) {
             const int item = item_at(k);
             if (item >= total_items) continue;
             const PrefillItem w = w_next;
             const int nxt = item_at(k + 1);
             if (!w.valid) {
-                if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+                if (nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);
                 continue;
             }
 #ifdef MFA_TRACE
@@ -740,7 +798,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
                                           : (int64_t)w.b * p.o_batch_stride + (int64_t)qrow * p.o_row_stride);
                 MFA_TRI(3 + i, 0);
 #ifndef MFA_NO_WNEXT
-                if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+                if (nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);
 #endif
                 if (n_mine > 0) {
                     mbar_wait(&o_full[i], (t_cnt + (uint32_t)n_mine - 1u) & 1u);
@@ -841,7 +899,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             }
             MFA_TRI(3 + i, 2);
 #ifdef MFA_NO_WNEXT
-            if (nxt < total_items) w_next = prefill_item<kNQ>(p, nxt);
+            if (nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);
 #endif
             t_cnt += (uint32_t)n_mine;
 #ifdef MFA_TRACE
@@ -863,7 +921,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
 
 }  // namespace
 
-template <typename T, int DPAD>
+template <typename T, int DPAD, bool kCompact>
 static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                     const PrefillKParams& p, cudaStream_t stream) {
     using Cfg = PrefillCfg<DPAD>;
@@ -871,7 +929,7 @@ static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& t
     // pipe as a degree-3 polynomial; it lost 2-4 % in every back-to-back measurement -- the board sits at its power cap
     // and the extra FMA work costs more clock than the relieved MUFU returns -- and was removed.  The packed
     // ex2.approx.f16x2 / bf16x2 forms are no way out either: ptxas splits them into two MUFU.EX2 per pair.)
-    auto kern = prefill_fwd_kernel<T, DPAD>;
+    auto kern = prefill_fwd_kernel<T, DPAD, kCompact>;
     static bool attr_done[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -911,8 +969,11 @@ cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const
                            const PrefillKParams& p, bool is_bf16, int dpad, cudaStream_t stream) {
 #define MFA_PREFILL_CASE(DP)                                                                     \
     case DP:                                                                                     \
-        return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP>(tmQ, tmK, tmV, p, stream)           \
-                       : launch_prefill_t<__half, DP>(tmQ, tmK, tmV, p, stream);
+        if (p.compact)                                                                           \
+            return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP, true>(tmQ, tmK, tmV, p, stream)     \
+                           : launch_prefill_t<__half, DP, true>(tmQ, tmK, tmV, p, stream);           \
+        return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP, false>(tmQ, tmK, tmV, p, stream)    \
+                       : launch_prefill_t<__half, DP, false>(tmQ, tmK, tmV, p, stream);
     switch (dpad) {
         MFA_PREFILL_CASE(64)
         MFA_PREFILL_CASE(128)

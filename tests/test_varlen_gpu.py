@@ -221,3 +221,46 @@ def test_packed_uniform_batch_runs_persistent(mfa, causal, dtype):
         r = R.attention_ref(q[b:b + 1, :lens[b]], k[b:b + 1, :lens[b]], v[b:b + 1, :lens[b]], causal)[0]
         assert (out2[off:off + lens[b]].float() - r).abs().max().item() <= TOL["fp16" if dtype == torch.float16 else "bf16"]
         off += lens[b]
+
+
+@pytest.mark.parametrize("seqlens", [
+    [0, 5, 300, 0, 1025],                               # empty sequences, unsorted lengths
+    [4096, 3, 3, 3, 3, 3, 3, 3],                        # one long sequence, many tiny ones
+    [random.Random(7).randint(1, 700) for _ in range(64)],   # the largest batch the item table holds
+    [random.Random(8).randint(1, 700) for _ in range(65)],   # one more: one CTA per item again
+    [256 * 3] * 2 + [256 * 3 + 1],                      # lengths on and one past an m-block boundary
+])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_ragged_causal_item_table(mfa, seqlens, dtype):
+    """Ragged causal packed batches of up to 64 sequences run persistent over a device-built table of the (m-block,
+    sequence) items that exist (prefill_sm100.cu: kCompact; capi.cu chooses): every row of every sequence must be
+    produced exactly once, whatever the lengths."""
+    from conftest import assert_close_16bit
+    from oracle import ref_attention as R
+    name = "fp16" if dtype == torch.float16 else "bf16"
+    for H, Hkv, D, seed in ((16, 4, 128, 3), (8, 8, 64, 4)):
+        g = torch.Generator(device="cuda").manual_seed(seed)
+        q = torch.randn(sum(seqlens), H, D, device="cuda", dtype=dtype, generator=g)
+        k = torch.randn(sum(seqlens), Hkv, D, device="cuda", dtype=dtype, generator=g)
+        v = torch.randn(sum(seqlens), Hkv, D, device="cuda", dtype=dtype, generator=g)
+        cu = _cu(seqlens)
+        out = mfa.flash_attn_varlen_func(q, k, v, cu, cu, max(seqlens), max(seqlens), causal=True)
+        assert out.shape == q.shape and torch.isfinite(out).all()
+        # (north_star bound + one ulp of the 16-bit output: the first causal rows copy V almost verbatim)
+        assert_close_16bit(out, R.varlen_ref(q, k, v, cu, cu, True), name)
+
+
+def test_ragged_causal_item_table_cross_lengths_and_paged(mfa):
+    """len_k != len_q (top-left causal like the reference) and the paged form of the same batch through the item table."""
+    _run_packed(mfa, [100, 700, 33, 1500], [300, 900, 33, 2000], 8, 2, 128, True, seed=5)
+    from oracle import ref_attention as R
+    sq = [100, 700, 33, 1500, 2048]
+    q, kc, vc, bt = _paged_inputs(sq, sq, 16, 4, 128, 64, torch.bfloat16, 6)
+    cu = _cu(sq)
+    kp = torch.cat([R.gather_paged(kc, bt[b], l) for b, l in enumerate(sq)])
+    vp = torch.cat([R.gather_paged(vc, bt[b], l) for b, l in enumerate(sq)])
+    a = mfa.flash_attn_varlen_func(q, kc, vc, cu, cu, max(sq), max(sq), causal=True, block_table=bt)
+    b = mfa.flash_attn_varlen_func(q, kp, vp, cu, cu, max(sq), max(sq), causal=True)
+    assert torch.equal(a, b)
+    ref = R.varlen_ref(q, kp, vp, cu, cu, True)
+    assert (b.float() - ref).abs().max().item() <= TOL["bf16"]
