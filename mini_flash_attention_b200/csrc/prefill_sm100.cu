@@ -246,11 +246,15 @@ __device__ __forceinline__ PrefillItem prefill_item(const PrefillKParams& p, int
 // kCompact: a separate instantiation for ragged causal packed batches (p.compact) -- the item decode of that form costs
 // the MMA-issuing warp registers and instructions, and the fixed-length kernel is sensitive to both (measured: with the
 // branch at run time the headline lost 3 %, causal 7 %).
-template <typename T, int DPAD, bool kCompact>
+// kMode 0: fixed-length batches and packed batches with one CTA per item -- the plain strided item walk, nothing else;
+// kMode 1: near-uniform packed batches, persistent, snake-order walk; kMode 2 (kCompact): ragged causal packed batches.
+// Compile-time, not p.snake / p.compact at run time: the strided walk of mode 0 is the code the headline was tuned on.
+template <typename T, int DPAD, int kMode>
 __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
     prefill_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const __grid_constant__ PrefillKParams p) {
     using Cfg = PrefillCfg<DPAD>;
+    constexpr bool kCompact = (kMode == 2);
     constexpr int kNQ = Cfg::kNQ;
     constexpr int kStages = Cfg::kStages;
     constexpr int kBM = Cfg::kBM, kBN = Cfg::kBN;
@@ -342,9 +346,14 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
     const int n_rounds = (total_items + (int)gridDim.x - 1) / (int)gridDim.x;
     auto item_at = [&](int k) -> int {   // total_items = this CTA has no item in round k
         if (k >= n_rounds) return total_items;
-        const int pos = (p.snake && (k & 1)) ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
+        const int pos = (kMode != 0 && (k & 1)) ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
         const int it = k * (int)gridDim.x + pos;
         return it < total_items ? it : total_items;
+    };
+    // (only the last round can leave a CTA without an item, so a walk may stop at the first miss)
+    auto next_item = [&](int k_next, int item) -> int {
+        if constexpr (kMode == 0) return item + (int)gridDim.x;
+        else return item_at(k_next);
     };
     constexpr uint32_t tmem_base = 0u;
 
@@ -365,9 +374,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
         uint32_t tail_phase = 0;
         int it = 0;                  // K/V ring position, runs across items
         uint32_t q_ld[2] = {0, 0};   // loads of Q tile i so far (parity base of q_full / q_empty)
-        for (int k = 0; k < n_rounds; ++k) {
-            const int item = item_at(k);
-            if (item >= total_items) continue;
+        for (int k = 0, item = blockIdx.x; item < total_items; ++k, item = next_item(k, item)) {
             const PrefillItem w = prefill_item<kNQ, kCompact>(p, item, sched);
             if (!w.valid) continue;
             const int q_row_coord = p.cu_seqlens_q ? (w.q_off + w.m0) : w.m0;
@@ -529,12 +536,10 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
             uint32_t t_cnt[2] = {0, 0};   // KV tiles done so far per Q tile (parity base of s_full / p_* / o_full)
             // The descriptor of the NEXT item (a handful of integer divisions, ~1000 cycles of dependent latency for a lone
             // warp) is computed while this warp waits for the last P of the current one, not between the items.
-            PrefillItem w_next = prefill_item<kNQ, kCompact>(p, item_at(0), sched);
-            for (int k = 0; k < n_rounds; ++k) {
-                const int item = item_at(k);
-                if (item >= total_items) continue;
+            PrefillItem w_next = prefill_item<kNQ, kCompact>(p, blockIdx.x, sched);
+            for (int k = 0, item = blockIdx.x; item < total_items; ++k, item = next_item(k, item)) {
                 const PrefillItem w = w_next;
-                const int nxt = item_at(k + 1);
+                const int nxt = next_item(k + 1, item);
                 if (!w.valid) {
                     if (nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);
                     continue;
@@ -625,12 +630,10 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
         const uint32_t tO = tmem_base + lane_sel + Cfg::kTmemO + i * DPAD;
         const float c2 = p.scale_log2;
         uint32_t t_cnt = 0;   // KV tiles this warpgroup has processed so far (parity base)
-        PrefillItem w_next = prefill_item<kNQ, kCompact>(p, item_at(0), sched);   // (computed under the epilogue's wait for the last P.V, see the MMA warp)
-        for (int k = 0; k < n_rounds; ++k) {
-            const int item = item_at(k);
-            if (item >= total_items) continue;
+        PrefillItem w_next = prefill_item<kNQ, kCompact>(p, blockIdx.x, sched);   // (computed under the epilogue's wait for the last P.V, see the MMA warp)
+        for (int k = 0, item = blockIdx.x; item < total_items; ++k, item = next_item(k, item)) {
             const PrefillItem w = w_next;
-            const int nxt = item_at(k + 1);
+            const int nxt = next_item(k + 1, item);
             if (!w.valid) {
                 if (nxt < total_items) w_next = prefill_item<kNQ, kCompact>(p, nxt, sched);
                 continue;
@@ -921,7 +924,7 @@ __global__ void __launch_bounds__(PrefillCfg<DPAD>::kThreads, 1)
 
 }  // namespace
 
-template <typename T, int DPAD, bool kCompact>
+template <typename T, int DPAD, int kMode>
 static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                     const PrefillKParams& p, cudaStream_t stream) {
     using Cfg = PrefillCfg<DPAD>;
@@ -929,7 +932,7 @@ static cudaError_t launch_prefill_t(const CUtensorMap& tmQ, const CUtensorMap& t
     // pipe as a degree-3 polynomial; it lost 2-4 % in every back-to-back measurement -- the board sits at its power cap
     // and the extra FMA work costs more clock than the relieved MUFU returns -- and was removed.  The packed
     // ex2.approx.f16x2 / bf16x2 forms are no way out either: ptxas splits them into two MUFU.EX2 per pair.)
-    auto kern = prefill_fwd_kernel<T, DPAD, kCompact>;
+    auto kern = prefill_fwd_kernel<T, DPAD, kMode>;
     static bool attr_done[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -970,10 +973,13 @@ cudaError_t launch_prefill(const CUtensorMap& tmQ, const CUtensorMap& tmK, const
 #define MFA_PREFILL_CASE(DP)                                                                     \
     case DP:                                                                                     \
         if (p.compact)                                                                           \
-            return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP, true>(tmQ, tmK, tmV, p, stream)     \
-                           : launch_prefill_t<__half, DP, true>(tmQ, tmK, tmV, p, stream);           \
-        return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP, false>(tmQ, tmK, tmV, p, stream)    \
-                       : launch_prefill_t<__half, DP, false>(tmQ, tmK, tmV, p, stream);
+            return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP, 2>(tmQ, tmK, tmV, p, stream)        \
+                           : launch_prefill_t<__half, DP, 2>(tmQ, tmK, tmV, p, stream);              \
+        if (p.snake)                                                                             \
+            return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP, 1>(tmQ, tmK, tmV, p, stream)        \
+                           : launch_prefill_t<__half, DP, 1>(tmQ, tmK, tmV, p, stream);              \
+        return is_bf16 ? launch_prefill_t<__nv_bfloat16, DP, 0>(tmQ, tmK, tmV, p, stream)        \
+                       : launch_prefill_t<__half, DP, 0>(tmQ, tmK, tmV, p, stream);
     switch (dpad) {
         MFA_PREFILL_CASE(64)
         MFA_PREFILL_CASE(128)
